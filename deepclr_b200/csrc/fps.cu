@@ -1,0 +1,193 @@
+// Farthest point sampling for sm_100a: one CTA per cloud, the cloud held in shared memory (SoA) and, per thread,
+// in registers; min-distance state never leaves registers; argmax = two redux.sync steps + one shared atomicMin.
+//
+// Replaces furthest_point_sampling_kernel + gather_points_kernel_fast of the reference
+// (extern/Pointnet2.PyTorch/pointnet2/src/sampling_gpu.cu:94-209, :8-24).  Arithmetic per round and point k is the
+// reference's (sampling_gpu.cu:133-137 as contracted by nvcc):
+//     d  = fma(dz,dz, fma(dx,dx, dy*dy)),  d* = p_k - p_old
+//     t_k = min(d, t_k)           (t_k starts at 1e10: pointnet2_utils.py:26)
+//     next = argmax_k t_k         ties -> LOWEST point index (BASELINE.json's stated rule)
+#include "common.cuh"
+#include "kernels.cuh"
+#include <limits.h>
+
+namespace dclr {
+
+constexpr int FPS_MAX_RESIDENT_N = 16384;
+
+// T threads, PPT points per thread (strided ownership k = tid + i*T), ZS: read z from shared memory instead of
+// registers (needed at T=1024, PPT=16 where only 64 registers per thread exist).
+template <int T, int PPT, bool ZS>
+__global__ void __launch_bounds__(T, 1)
+fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int32_t *__restrict__ idx_out,
+                    float *__restrict__ new_xyz_out) {
+    extern __shared__ __align__(16) float smem[];
+    float *s_x = smem, *s_y = smem + N, *s_z = smem + 2 * N;
+    int *s_wmax = reinterpret_cast<int *>(smem + 3 * N);   // [32]
+    int *s_win = s_wmax + 32;                              // [2]
+
+    const int b = blockIdx.x;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    pts += (size_t)b * N * stride;
+    idx_out += (size_t)b * npoint;
+    if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
+
+    // stage the cloud: coalesced (float4 when the point stride is 4 floats)
+    if (stride == 4) {
+        const float4 *p4 = reinterpret_cast<const float4 *>(pts);
+        for (int k = tid; k < N; k += T) {
+            float4 v = __ldg(p4 + k);
+            s_x[k] = v.x; s_y[k] = v.y; s_z[k] = v.z;
+        }
+    } else {
+        for (int k = tid; k < N; k += T) {
+            const float *p = pts + (size_t)k * stride;
+            s_x[k] = __ldg(p); s_y[k] = __ldg(p + 1); s_z[k] = __ldg(p + 2);
+        }
+    }
+    if (tid < 2) s_win[tid] = INT_MAX;
+    __syncthreads();
+
+    float x[PPT], y[PPT], z[ZS ? 1 : PPT], t[PPT];
+#pragma unroll
+    for (int i = 0; i < PPT; ++i) {
+        int k = tid + i * T;
+        bool ok = k < N;
+        x[i] = ok ? s_x[k] : 0.f;
+        y[i] = ok ? s_y[k] : 0.f;
+        if (!ZS) z[i] = ok ? s_z[k] : 0.f;
+        t[i] = ok ? 1e10f : -1.0f;     // -1 can never win (reference: best starts at -1, strict >)
+    }
+
+    int old = 0;
+    if (tid == 0) idx_out[0] = 0;
+    for (int j = 1; j < npoint; ++j) {
+        const float x1 = s_x[old], y1 = s_y[old], z1 = s_z[old];
+        if (tid == 0 && new_xyz_out) {
+            new_xyz_out[(j - 1) * 3 + 0] = x1; new_xyz_out[(j - 1) * 3 + 1] = y1; new_xyz_out[(j - 1) * 3 + 2] = z1;
+        }
+        float best = -1.0f;
+#pragma unroll
+        for (int i = 0; i < PPT; ++i) {
+            float zz;
+            if (ZS) { int k = tid + i * T; zz = s_z[k < N ? k : 0]; } else zz = z[i];
+            float d = sqdist_pn2(x[i] - x1, y[i] - y1, zz - z1);
+            t[i] = fminf(d, t[i]);
+            best = fmaxf(best, t[i]);
+        }
+        // block max of the (non-negative) float through its integer image
+        int wb = __reduce_max_sync(0xffffffffu, __float_as_int(best));
+        if (lane == 0) s_wmax[warp] = wb;
+        __syncthreads();
+        int v = lane < (T / 32) ? s_wmax[lane] : INT_MIN;
+        const int m = __reduce_max_sync(0xffffffffu, v);
+        if (tid == 0) s_win[(j + 1) & 1] = INT_MAX;          // re-arm the other slot for the next round
+        if (__float_as_int(best) == m) {
+            int cand = INT_MAX;
+#pragma unroll
+            for (int i = PPT - 1; i >= 0; --i)
+                if (__float_as_int(t[i]) == m) cand = tid + i * T;   // lowest i (= lowest index) survives
+            atomicMin(&s_win[j & 1], cand);
+        }
+        __syncthreads();
+        old = s_win[j & 1];
+        if (tid == 0) idx_out[j] = old;
+    }
+    if (tid == 0 && new_xyz_out && npoint > 0) {
+        new_xyz_out[(npoint - 1) * 3 + 0] = s_x[old];
+        new_xyz_out[(npoint - 1) * 3 + 1] = s_y[old];
+        new_xyz_out[(npoint - 1) * 3 + 2] = s_z[old];
+    }
+}
+
+// Clouds too large for one SM's shared memory: state streamed from global/L2 each round (same arithmetic and
+// tie-break).  temp: [B,N] scratch.
+template <int T>
+__global__ void __launch_bounds__(T, 1)
+fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, float *__restrict__ temp,
+                  int32_t *__restrict__ idx_out, float *__restrict__ new_xyz_out) {
+    __shared__ int s_wmax[32];
+    __shared__ int s_win[2];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pts += (size_t)b * N * stride;
+    temp += (size_t)b * N;
+    idx_out += (size_t)b * npoint;
+    if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
+    for (int k = tid; k < N; k += T) temp[k] = 1e10f;
+    if (tid < 2) s_win[tid] = INT_MAX;
+    __syncthreads();
+    int old = 0;
+    if (tid == 0) idx_out[0] = 0;
+    for (int j = 1; j <= npoint; ++j) {
+        const float x1 = __ldg(pts + (size_t)old * stride), y1 = __ldg(pts + (size_t)old * stride + 1),
+                    z1 = __ldg(pts + (size_t)old * stride + 2);
+        if (tid == 0 && new_xyz_out) {
+            new_xyz_out[(j - 1) * 3 + 0] = x1; new_xyz_out[(j - 1) * 3 + 1] = y1; new_xyz_out[(j - 1) * 3 + 2] = z1;
+        }
+        if (j == npoint) break;
+        float best = -1.0f;
+        int besti = INT_MAX;
+        for (int k = tid; k < N; k += T) {
+            const float *p = pts + (size_t)k * stride;
+            float d = sqdist_pn2(__ldg(p) - x1, __ldg(p + 1) - y1, __ldg(p + 2) - z1);
+            float d2 = fminf(d, temp[k]);
+            temp[k] = d2;
+            if (d2 > best) { best = d2; besti = k; }      // strict >: lowest k of this thread
+        }
+        int wb = __reduce_max_sync(0xffffffffu, __float_as_int(best));
+        if (lane == 0) s_wmax[warp] = wb;
+        __syncthreads();
+        int v = lane < (T / 32) ? s_wmax[lane] : INT_MIN;
+        const int m = __reduce_max_sync(0xffffffffu, v);
+        if (tid == 0) s_win[(j + 1) & 1] = INT_MAX;
+        if (__float_as_int(best) == m) atomicMin(&s_win[j & 1], besti);
+        __syncthreads();
+        old = s_win[j & 1];
+        if (tid == 0) idx_out[j] = old;
+    }
+}
+
+template <int T, int PPT, bool ZS>
+static int launch_resident(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx,
+                           cudaStream_t st) {
+    size_t smem = (size_t)3 * N * sizeof(float) + 34 * sizeof(int);
+    auto kern = fps_resident_kernel<T, PPT, ZS>;
+    DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<B, T, smem, st>>>(pts, stride, N, npoint, idx, nx);
+    DCLR_LAUNCH_CHECK("fps_resident_kernel");
+    return DCLR_OK;
+}
+
+int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, float *temp_big,
+               cudaStream_t st) {
+    if (N <= 128) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 256) return launch_resident<128, 2, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 512) return launch_resident<128, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 1024) return launch_resident<128, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 2048) return launch_resident<256, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 4096) return launch_resident<256, 16, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 8192) return launch_resident<512, 16, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= FPS_MAX_RESIDENT_N) return launch_resident<1024, 16, true>(pts, stride, B, N, npoint, idx, nx, st);
+    if (!temp_big) return fail(DCLR_E_INVALID, "fps: N=%d needs a scratch buffer", N);
+    fps_stream_kernel<1024><<<B, 1024, 0, st>>>(pts, stride, N, npoint, temp_big, idx, nx);
+    DCLR_LAUNCH_CHECK("fps_stream_kernel");
+    return DCLR_OK;
+}
+
+}  // namespace dclr
+
+extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int32_t *idx_out,
+                        float *new_xyz_out, void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(pts && idx_out, "dclr_fps: null pointer");
+    DCLR_CHECK_ARG(pt_stride >= 3 && B >= 0 && N >= 1 && npoint >= 0, "dclr_fps: bad shape B=%d N=%d npoint=%d stride=%d",
+                   B, N, npoint, pt_stride);
+    if (B == 0 || npoint == 0) return DCLR_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *temp = nullptr;
+    if (N > FPS_MAX_RESIDENT_N) DCLR_CUDA(cudaMallocAsync(&temp, (size_t)B * N * sizeof(float), st));
+    int rc = fps_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, temp, st);
+    if (temp) cudaFreeAsync(temp, st);
+    return rc;
+}

@@ -1,0 +1,46 @@
+// Internal launch interfaces between the translation units of libdeepclr_b200.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace dclr {
+
+// fps.cu
+int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, float *temp_big,
+               cudaStream_t st);
+
+// pointops.cu
+int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
+                      const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad,
+                      cudaStream_t st);
+int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
+               int32_t *col_local, cudaStream_t st);
+
+// sa_mlp.cu
+struct SaArgs {
+    const float *x;          // [B,N,C] points (xyz + features), C = CIN
+    const float *new_xyz;    // [B,M,3]
+    const int32_t *idx[2];   // compact neighbour lists [B,M,ns]
+    const int32_t *cnt[2];   // [B,M]
+    int ns[2];
+    const float *w[2];       // per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
+    float *out;              // [B,M,ld_out] point-major; scale s writes columns [s*H3, (s+1)*H3)
+    int N, M, ld_out, nscales;
+};
+int sa_mlp_launch(const SaArgs &a, int B, int cin, const int *h, cudaStream_t st);
+
+// dense_f32.cu
+int linear_f32_launch(const float *X, int ldx, const float *W, const float *b, float *Y, int ldy, int M, int N, int K,
+                      int relu, cudaStream_t st);
+int flow_rows_launch(const float *xyz, const float *feat, const int32_t *nbr, int B, int n, int k, int F, float radius,
+                     float *rows, int ld, uint8_t *mask, cudaStream_t st);
+int masked_groupmax_launch(const float *H, int ldh, const uint8_t *mask, const float *xyz, size_t groups, int k, int C,
+                           float *out, int ldo, cudaStream_t st);
+int rowmax_launch(const float *H, int ldh, int B, int n, int C, float *out, cudaStream_t st);
+int pose_activation_launch(float *y, int B, int dim, int label_type, cudaStream_t st);
+int pm_to_cm_launch(const float *xyz, const float *feat, int ldf, int off, int G, int n, int F, float *out,
+                    cudaStream_t st);
+int cm_to_pm_launch(const float *in, int G, int n, int F, float *xyz, float *feat, cudaStream_t st);
+
+}  // namespace dclr

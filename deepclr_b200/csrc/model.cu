@@ -1,0 +1,304 @@
+// Model handle + forward orchestration: the C-ABI face of DeepCLR.forward / cloud_features
+// (reference deepclr/models/deepclr.py:488-521).  One call enqueues the whole chain on the caller's stream.
+#include "common.cuh"
+#include "kernels.cuh"
+#include "mlp_tc.cuh"
+#include <new>
+#include <vector>
+
+struct dclr_model {
+    dclr_arch arch;
+    int label_dim, F, nmerge_in, head_in;
+    float *d_w = nullptr;            // all parameters, state-dict order
+    size_t n_w = 0;
+    const float *sa_w[2] = {nullptr, nullptr};
+    struct Lin { const float *W, *b; int out, in; };
+    Lin merge[3], outc[5], lin[2], fin;
+    int numerics = 0;
+    // workspace
+    void *ws = nullptr;
+    size_t ws_bytes = 0;
+    int last_launches = 0;
+    // carved pointers (valid after ensure_ws)
+    int32_t *fps_idx, *bq_idx[2], *bq_cnt[2], *knn_col;
+    float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
+    uint8_t *mask;
+    dclr::TcModel *tc = nullptr;     // bf16 tensor-core path (mlp_tc.cu)
+};
+
+namespace dclr {
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int label_dim_of(int t) { return t == 0 ? 6 : (t == 1 ? 7 : 8); }
+
+// carve (or just measure when base == nullptr) the workspace for G clouds of N points / B pairs
+static size_t carve(dclr_model *m, char *base, int G, int N, int B) {
+    const dclr_arch &a = m->arch;
+    const int M = a.npoint;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off = align_up(off + bytes, 256); return p; };
+    m->fps_idx = (int32_t *)take((size_t)G * M * 4);
+    m->new_xyz = (float *)take((size_t)G * M * 3 * 4);
+    for (int s = 0; s < 2; ++s) {
+        int ns = s < a.num_scales ? a.nsamples[s] : 0;
+        m->bq_idx[s] = (int32_t *)take((size_t)G * M * ns * 4);
+        m->bq_cnt[s] = (int32_t *)take((size_t)G * M * 4);
+    }
+    m->sa_feat = (float *)take((size_t)G * M * m->F * 4);
+    m->fps_temp = (float *)take(N > 16384 ? (size_t)G * N * 4 : 0);
+    const size_t BM = (size_t)B * M;
+    const size_t R = BM * (a.knn_k > 0 ? a.knn_k : 1);
+    m->knn_col = (int32_t *)take(R * 4);
+    m->motion = (float *)take(BM * align_up(3 + a.merge_mlp[2], 4) * 4);
+    m->pooled = (float *)take((size_t)B * a.out_mlp[4] * 4);
+    m->t1 = (float *)take((size_t)B * a.out_linear[1] * 4);
+    m->t2 = (float *)take((size_t)B * a.out_linear[2] * 4);
+    if (m->numerics == 0) {
+        int wmax = 0;
+        for (int i = 0; i < 5; ++i) wmax = a.out_mlp[i] > wmax ? a.out_mlp[i] : wmax;
+        m->rows = (float *)take(R * align_up(m->nmerge_in, 4) * 4);
+        m->h1 = (float *)take(R * a.merge_mlp[0] * 4);
+        m->h2 = (float *)take(R * a.merge_mlp[1] * 4);
+        m->h3 = (float *)take(R * a.merge_mlp[2] * 4);
+        m->mask = (uint8_t *)take(R);
+        m->actA = (float *)take(BM * wmax * 4);
+        m->actB = (float *)take(BM * wmax * 4);
+    } else {
+        m->rows = m->h1 = m->h2 = m->h3 = m->actA = m->actB = nullptr;
+        m->mask = nullptr;
+    }
+    return off;
+}
+
+static int ensure_ws(dclr_model *m, int G, int N, int B) {
+    size_t need = carve(m, nullptr, G, N, B);
+    if (need > m->ws_bytes) {
+        if (m->ws) DCLR_CUDA(cudaFree(m->ws));
+        m->ws = nullptr;
+        m->ws_bytes = 0;
+        DCLR_CUDA(cudaMalloc(&m->ws, need));
+        m->ws_bytes = need;
+    }
+    carve(m, (char *)m->ws, G, N, B);
+    return DCLR_OK;
+}
+
+#define DCLR_TRY(expr)            \
+    do {                          \
+        int rc__ = (expr);        \
+        if (rc__ != DCLR_OK) return rc__; \
+        ++m->last_launches;       \
+    } while (0)
+
+// FPS -> ball query (both radii, one pass) -> grouped MLP + max-pool.  pointnet2_modules.py:19-55
+static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cudaStream_t st) {
+    const dclr_arch &a = m->arch;
+    DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+    DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
+                               m->bq_idx, m->bq_cnt, /*pad=*/0, st));
+    SaArgs s;
+    s.x = x; s.new_xyz = m->new_xyz; s.N = N; s.M = a.npoint; s.ld_out = m->F; s.nscales = a.num_scales;
+    s.out = m->sa_feat;
+    for (int i = 0; i < 2; ++i) {
+        s.idx[i] = m->bq_idx[i]; s.cnt[i] = m->bq_cnt[i]; s.ns[i] = a.nsamples[i < a.num_scales ? i : 0];
+        s.w[i] = m->sa_w[i];
+    }
+    DCLR_TRY(sa_mlp_launch(s, G, a.input_dim, a.sa_mlp[0], st));
+    return DCLR_OK;
+}
+
+// kNN grouping + motion embedding + output head on point-major SA features.  deepclr.py:157-231, 284-294
+static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_out, cudaStream_t st) {
+    const dclr_arch &a = m->arch;
+    const int M = a.npoint, k = a.knn_k, F = m->F;
+    const size_t BM = (size_t)B * M, R = BM * k;
+    const int ldm = (int)align_up(3 + a.merge_mlp[2], 4);
+    // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
+    DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, st));
+    if (m->numerics == 1) {
+        int rc = tc_merge_output(m->tc, m->new_xyz, m->sa_feat, m->knn_col, B, M, m->motion, ldm, m->pooled, st,
+                                 &m->last_launches);
+        if (rc != DCLR_OK) return rc;
+    } else {
+        const int ld0 = (int)align_up(m->nmerge_in, 4);
+        DCLR_TRY(flow_rows_launch(m->new_xyz, m->sa_feat, m->knn_col, B, M, k, F, a.merge_radius, m->rows, ld0,
+                                  m->mask, st));
+        DCLR_TRY(linear_f32_launch(m->rows, ld0, m->merge[0].W, m->merge[0].b, m->h1, a.merge_mlp[0], (int)R,
+                                   a.merge_mlp[0], m->nmerge_in, 1, st));
+        DCLR_TRY(linear_f32_launch(m->h1, a.merge_mlp[0], m->merge[1].W, m->merge[1].b, m->h2, a.merge_mlp[1], (int)R,
+                                   a.merge_mlp[1], a.merge_mlp[0], 1, st));
+        DCLR_TRY(linear_f32_launch(m->h2, a.merge_mlp[1], m->merge[2].W, m->merge[2].b, m->h3, a.merge_mlp[2], (int)R,
+                                   a.merge_mlp[2], a.merge_mlp[1], 1, st));
+        DCLR_TRY(masked_groupmax_launch(m->h3, a.merge_mlp[2], m->mask, m->new_xyz, BM, k, a.merge_mlp[2], m->motion,
+                                        ldm, st));
+        const float *in = m->motion;
+        int ldin = ldm, kin = m->head_in;
+        float *bufs[2] = {m->actA, m->actB};
+        for (int l = 0; l < 5; ++l) {
+            float *out = bufs[l & 1];
+            DCLR_TRY(linear_f32_launch(in, ldin, m->outc[l].W, m->outc[l].b, out, a.out_mlp[l], (int)BM, a.out_mlp[l],
+                                       kin, 1, st));
+            in = out; ldin = a.out_mlp[l]; kin = a.out_mlp[l];
+        }
+        DCLR_TRY(rowmax_launch(in, ldin, B, M, a.out_mlp[4], m->pooled, st));
+    }
+    // fully connected tail: helper.py:97-123 (ReLU after both), final nn.Linear, activation deepclr.py:275-282
+    DCLR_TRY(linear_f32_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
+                               a.out_linear[1], a.out_linear[0], 1, st));
+    DCLR_TRY(linear_f32_launch(m->t1, a.out_linear[1], m->lin[1].W, m->lin[1].b, m->t2, a.out_linear[2], B,
+                               a.out_linear[2], a.out_linear[1], 1, st));
+    DCLR_TRY(linear_f32_launch(m->t2, a.out_linear[2], m->fin.W, m->fin.b, y_out, m->label_dim, B, m->label_dim,
+                               a.out_linear[2], 0, st));
+    DCLR_TRY(pose_activation_launch(y_out, B, m->label_dim, a.label_type, st));
+    if (motion_out)
+        DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, ldm, 0, B, M, a.merge_mlp[2], motion_out, st));
+    return DCLR_OK;
+}
+
+}  // namespace dclr
+
+// ------------------------------------------------------------------ C ABI
+using namespace dclr;
+
+extern "C" int dclr_model_create(const dclr_arch *arch, const float *weights, size_t num_floats, dclr_model **out) {
+    DCLR_CHECK_ARG(arch && weights && out, "dclr_model_create: null pointer");
+    const dclr_arch &a = *arch;
+    DCLR_CHECK_ARG(a.input_dim == 3 || a.input_dim == 4, "input_dim must be 3 or 4 (got %d)", a.input_dim);
+    DCLR_CHECK_ARG(a.num_scales == 1 || a.num_scales == 2, "num_scales must be 1 or 2");
+    DCLR_CHECK_ARG(a.npoint >= 1 && a.knn_k >= 1 && a.knn_k <= 128, "need npoint >= 1 and 1 <= k <= 128");
+    DCLR_CHECK_ARG(a.label_type >= 0 && a.label_type <= 2, "label_type must be 0..2");
+    DCLR_CHECK_ARG(a.out_linear[0] == a.out_mlp[4], "out_linear[0] must equal out_mlp[4]");
+    dclr_model *m = new (std::nothrow) dclr_model();
+    DCLR_CHECK_ARG(m, "out of host memory");
+    m->arch = a;
+    m->label_dim = label_dim_of(a.label_type);
+    m->F = 0;
+    for (int s = 0; s < a.num_scales; ++s) m->F += a.sa_mlp[s][2];
+    m->nmerge_in = 3 + 2 * m->F;                 // append_features=True (deepclr.py:193-194)
+    m->head_in = 3 + a.merge_mlp[2];
+    // walk the state-dict order and record offsets
+    size_t off = 0;
+    std::vector<size_t> w_off, b_off;
+    auto add = [&](int o, int i) { w_off.push_back(off); off += (size_t)o * i; b_off.push_back(off); off += o; };
+    size_t sa_off[2] = {0, 0};
+    for (int s = 0; s < a.num_scales; ++s) {
+        sa_off[s] = off;
+        int cin = a.input_dim;                   // (input_dim - 3) features + 3 xyz (pointnet2_modules.py:88-89)
+        for (int l = 0; l < 3; ++l) { add(a.sa_mlp[s][l], cin); cin = a.sa_mlp[s][l]; }
+    }
+    size_t first_dense = w_off.size();
+    int cin = m->nmerge_in;
+    for (int l = 0; l < 3; ++l) { add(a.merge_mlp[l], cin); cin = a.merge_mlp[l]; }
+    cin = m->head_in;
+    for (int l = 0; l < 5; ++l) { add(a.out_mlp[l], cin); cin = a.out_mlp[l]; }
+    for (int l = 0; l < 2; ++l) add(a.out_linear[l + 1], a.out_linear[l]);
+    add(m->label_dim, a.out_linear[2]);
+    if (off != num_floats) {
+        delete m;
+        return fail(DCLR_E_INVALID, "dclr_model_create: expected %zu parameters for this architecture, got %zu", off,
+                    num_floats);
+    }
+    cudaError_t e = cudaMalloc(&m->d_w, off * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(m->d_w, weights, off * sizeof(float), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        if (m->d_w) cudaFree(m->d_w);
+        delete m;
+        return fail(DCLR_E_CUDA, "dclr_model_create: %s", cudaGetErrorString(e));
+    }
+    m->n_w = off;
+    for (int s = 0; s < a.num_scales; ++s) m->sa_w[s] = m->d_w + sa_off[s];
+    size_t q = first_dense;
+    auto lin = [&](int o, int i) { dclr_model::Lin L{m->d_w + w_off[q], m->d_w + b_off[q], o, i}; ++q; return L; };
+    cin = m->nmerge_in;
+    for (int l = 0; l < 3; ++l) { m->merge[l] = lin(a.merge_mlp[l], cin); cin = a.merge_mlp[l]; }
+    cin = m->head_in;
+    for (int l = 0; l < 5; ++l) { m->outc[l] = lin(a.out_mlp[l], cin); cin = a.out_mlp[l]; }
+    for (int l = 0; l < 2; ++l) m->lin[l] = lin(a.out_linear[l + 1], a.out_linear[l]);
+    m->fin = lin(m->label_dim, a.out_linear[2]);
+    *out = m;
+    return DCLR_OK;
+}
+
+extern "C" void dclr_model_destroy(dclr_model *m) {
+    if (!m) return;
+    if (m->tc) tc_destroy(m->tc);
+    if (m->ws) cudaFree(m->ws);
+    if (m->d_w) cudaFree(m->d_w);
+    delete m;
+}
+
+extern "C" int dclr_model_set_numerics(dclr_model *m, int mode) {
+    DCLR_CHECK_ARG(m, "null model");
+    DCLR_CHECK_ARG(mode == 0 || mode == 1, "numerics mode must be 0 (fp32) or 1 (bf16 tensor cores)");
+    if (mode == 1 && !m->tc) {
+        TcLayerSpec specs[8];
+        for (int l = 0; l < 3; ++l) specs[l] = {m->merge[l].W, m->merge[l].b, m->merge[l].out, m->merge[l].in};
+        for (int l = 0; l < 5; ++l) specs[3 + l] = {m->outc[l].W, m->outc[l].b, m->outc[l].out, m->outc[l].in};
+        int rc = tc_create(specs, m->F, m->arch.knn_k, m->arch.merge_radius, &m->tc);
+        if (rc != DCLR_OK) return rc;
+    }
+    m->numerics = mode;
+    return DCLR_OK;
+}
+
+extern "C" int dclr_cloud_features(dclr_model *m, const float *x, int num_clouds, int N, float *feat_out,
+                                   void *stream) {
+    DCLR_CHECK_ARG(m && x && feat_out, "dclr_cloud_features: null pointer");
+    DCLR_CHECK_ARG(num_clouds >= 1 && N >= 1, "dclr_cloud_features: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    m->last_launches = 0;
+    int rc = ensure_ws(m, num_clouds, N, (num_clouds + 1) / 2);
+    if (rc != DCLR_OK) return rc;
+    rc = run_set_abstraction(m, x, num_clouds, N, st);
+    if (rc != DCLR_OK) return rc;
+    DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->sa_feat, m->F, 0, num_clouds, m->arch.npoint, m->F, feat_out, st));
+    return DCLR_OK;
+}
+
+extern "C" int dclr_forward_features(dclr_model *m, const float *feat, int B, float *y_out, float *motion_out,
+                                     void *stream) {
+    DCLR_CHECK_ARG(m && feat && y_out, "dclr_forward_features: null pointer");
+    DCLR_CHECK_ARG(B >= 1, "dclr_forward_features: bad batch");
+    DCLR_CHECK_ARG(m->arch.knn_k <= m->arch.npoint, "knn k=%d exceeds npoint=%d", m->arch.knn_k, m->arch.npoint);
+    cudaStream_t st = (cudaStream_t)stream;
+    m->last_launches = 0;
+    int rc = ensure_ws(m, 2 * B, 1, B);
+    if (rc != DCLR_OK) return rc;
+    DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, st));
+    return run_merge_output(m, B, y_out, motion_out, st);
+}
+
+extern "C" int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, float *y_out, float *feat_out,
+                                  float *motion_out, void *stream) {
+    DCLR_CHECK_ARG(m && x && y_out, "dclr_forward_pairs: null pointer");
+    DCLR_CHECK_ARG(B >= 1 && N >= 1, "dclr_forward_pairs: bad shape");
+    DCLR_CHECK_ARG(m->arch.knn_k <= m->arch.npoint, "knn k=%d exceeds npoint=%d", m->arch.knn_k, m->arch.npoint);
+    cudaStream_t st = (cudaStream_t)stream;
+    m->last_launches = 0;
+    int rc = ensure_ws(m, 2 * B, N, B);
+    if (rc != DCLR_OK) return rc;
+    rc = run_set_abstraction(m, x, 2 * B, N, st);
+    if (rc != DCLR_OK) return rc;
+    if (feat_out)
+        DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->sa_feat, m->F, 0, 2 * B, m->arch.npoint, m->F, feat_out, st));
+    return run_merge_output(m, B, y_out, motion_out, st);
+}
+
+extern "C" int dclr_model_last_launches(const dclr_model *m) { return m ? m->last_launches : 0; }
+
+extern "C" int dclr_model_debug_copy(const dclr_model *m, int which, void *dst, size_t nbytes, void *stream) {
+    DCLR_CHECK_ARG(m && m->ws && dst, "dclr_model_debug_copy: no workspace yet or null dst");
+    const void *src = nullptr;
+    switch (which) {
+        case 0: src = m->fps_idx; break;
+        case 1: src = m->bq_cnt[0]; break;
+        case 2: src = m->bq_cnt[1]; break;
+        case 3: src = m->knn_col; break;
+        case 4: src = m->bq_idx[0]; break;
+        case 5: src = m->bq_idx[1]; break;
+        default: return fail(DCLR_E_INVALID, "dclr_model_debug_copy: unknown tap %d", which);
+    }
+    DCLR_CUDA(cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return DCLR_OK;
+}

@@ -1,0 +1,342 @@
+// gather / group / ball query / kNN for sm_100a.
+//
+// ball query: replaces ball_query_kernel_fast (extern/Pointnet2.PyTorch/pointnet2/src/ball_query_gpu.cu:9-45).  The
+// reference runs one thread per centre over all N points with strided scalar loads; here a warp owns CPW centres,
+// its lanes take 32 consecutive points of a tile that the TMA engine (cp.async.bulk, mbarrier-tracked, double
+// buffered) staged into shared memory, and hits are compacted in index order with ballot/popc, so the result is the
+// reference's "first nsample hits in ascending index order".  Up to two radii share one distance pass.
+//
+// kNN: replaces torch_cluster.knn as called at deepclr/models/deepclr.py:164-166; a warp owns one query, candidates
+// are packed as (float bits of d^2 << 32 | index) so a u64 minimum is "nearest, lowest index on ties".
+#include "common.cuh"
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace dclr {
+
+// ------------------------------------------------------------------ gather / group (compat ops)
+__global__ void gather_kernel(const float *__restrict__ feat, const int32_t *__restrict__ idx, int C, int N, int M,
+                              float *__restrict__ out) {
+    int b = blockIdx.z, c = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= M) return;
+    out[((size_t)b * C + c) * M + j] = __ldg(feat + ((size_t)b * C + c) * N + __ldg(idx + (size_t)b * M + j));
+}
+
+__global__ void group_kernel(const float *__restrict__ feat, const int32_t *__restrict__ idx, int C, int N, int M,
+                             int ns, float *__restrict__ out) {
+    int b = blockIdx.z, c = blockIdx.y;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // over M*ns
+    if (e >= (size_t)M * ns) return;
+    out[((size_t)b * C + c) * M * ns + e] = __ldg(feat + ((size_t)b * C + c) * N + __ldg(idx + (size_t)b * M * ns + e));
+}
+
+// ------------------------------------------------------------------ ball query
+constexpr int BQ_TILE = 2048;     // points per stage
+constexpr int BQ_WARPS = 8;
+
+struct BqArgs {
+    const float *new_xyz;   // [B,M,3]
+    const float *pts;       // [B,N,stride]
+    int stride, N, M;
+    float r2[2];
+    int ns[2];
+    int32_t *idx[2];        // [B,M,ns]
+    int32_t *cnt[2];        // [B,M] nullable
+    int pad;
+};
+
+template <int NR, int CPW>
+__global__ void __launch_bounds__(BQ_WARPS * 32)
+ball_query_kernel(BqArgs a) {
+    extern __shared__ __align__(128) float bq_smem[];
+    __shared__ __align__(8) uint64_t bars[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y;
+    const int N = a.N, M = a.M, stride = a.stride;
+    const float *pts = a.pts + (size_t)b * N * stride;
+    const bool bulk = (stride == 4 || stride == 3) && ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) &&
+                      (((size_t)N * stride * 4) % 16 == 0);
+    const int ss = bulk ? stride : 3;                 // point stride in shared memory
+    float *buf0 = bq_smem, *buf1 = bq_smem + BQ_TILE * 4;
+    const int ntiles = (N + BQ_TILE - 1) / BQ_TILE;
+
+    if (tid == 0) {
+        ptx::mbar_init(&bars[0], 1);
+        ptx::mbar_init(&bars[1], 1);
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+    auto issue = [&](int t) {   // one thread: stage tile t
+        int cntp = min(BQ_TILE, N - t * BQ_TILE);
+        uint32_t bytes = (uint32_t)cntp * stride * 4;
+        ptx::mbar_expect_tx(&bars[t & 1], bytes);
+        ptx::bulk_g2s((t & 1) ? buf1 : buf0, pts + (size_t)t * BQ_TILE * stride, bytes, &bars[t & 1]);
+    };
+    if (bulk && tid == 0) issue(0);
+
+    // centres of this warp
+    const int c0 = (blockIdx.x * BQ_WARPS + warp) * CPW;
+    float cx[CPW], cy[CPW], cz[CPW];
+    int cnt[CPW][NR], first[CPW][NR];
+#pragma unroll
+    for (int ci = 0; ci < CPW; ++ci) {
+        int c = c0 + ci;
+        const float *q = a.new_xyz + ((size_t)b * M + (c < M ? c : 0)) * 3;
+        cx[ci] = __ldg(q); cy[ci] = __ldg(q + 1); cz[ci] = __ldg(q + 2);
+#pragma unroll
+        for (int r = 0; r < NR; ++r) { cnt[ci][r] = (c < M) ? 0 : 0x40000000; first[ci][r] = 0; }
+    }
+    float r2max = a.r2[0];
+    if (NR > 1) r2max = fmaxf(r2max, a.r2[1]);
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    for (int t = 0; t < ntiles; ++t) {
+        const int base = t * BQ_TILE;
+        const int tile_cnt = min(BQ_TILE, N - base);
+        float *buf = (t & 1) ? buf1 : buf0;
+        if (bulk) {
+            if (tid == 0 && t + 1 < ntiles) issue(t + 1);
+            ptx::mbar_wait(&bars[t & 1], (t >> 1) & 1);
+        } else {
+            for (int k = tid; k < tile_cnt; k += BQ_WARPS * 32) {
+                const float *p = pts + (size_t)(base + k) * stride;
+                buf[k * 3 + 0] = __ldg(p); buf[k * 3 + 1] = __ldg(p + 1); buf[k * 3 + 2] = __ldg(p + 2);
+            }
+            __syncthreads();
+        }
+        bool done = true;
+#pragma unroll
+        for (int ci = 0; ci < CPW; ++ci)
+#pragma unroll
+            for (int r = 0; r < NR; ++r) done = done && (cnt[ci][r] >= a.ns[r]);
+        if (!done) {
+            for (int s = 0; s < tile_cnt; s += 32) {
+                const int kk = s + lane;
+                const bool valid = kk < tile_cnt;
+                float px = 0.f, py = 0.f, pz = 0.f;
+                if (valid) {
+                    if (ss == 4) {
+                        float4 v = *reinterpret_cast<const float4 *>(buf + kk * 4);
+                        px = v.x; py = v.y; pz = v.z;
+                    } else {
+                        px = buf[kk * 3]; py = buf[kk * 3 + 1]; pz = buf[kk * 3 + 2];
+                    }
+                }
+#pragma unroll
+                for (int ci = 0; ci < CPW; ++ci) {
+                    // operand order of the reference: (new - x), ball_query_gpu.cu:33
+                    const float d2 = sqdist_pn2(cx[ci] - px, cy[ci] - py, cz[ci] - pz);
+                    const bool h = valid && (d2 < r2max);
+                    const unsigned any = __ballot_sync(0xffffffffu, h);
+                    if (any) {
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) {
+                            const bool hr = h && (d2 < a.r2[r]);
+                            const unsigned mr = (NR == 1) ? any : __ballot_sync(0xffffffffu, hr);
+                            if (mr) {
+                                const int pos = cnt[ci][r] + __popc(mr & lt_mask);
+                                if (hr && pos < a.ns[r])
+                                    a.idx[r][((size_t)b * M + c0 + ci) * a.ns[r] + pos] = base + kk;
+                                if (cnt[ci][r] == 0) first[ci][r] = base + s + __ffs(mr) - 1;
+                                cnt[ci][r] += __popc(mr);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();   // all warps finished with this buffer before it is refilled
+    }
+
+    // epilogue: counts + padding (ball_query_gpu.cu:35-39: every slot is pre-filled with the first hit; empty ball =
+    // caller's zeros, pointnet2_utils.py:218)
+#pragma unroll
+    for (int ci = 0; ci < CPW; ++ci) {
+        const int c = c0 + ci;
+        if (c >= M) continue;
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const int n = min(cnt[ci][r], a.ns[r]);
+            if (a.cnt[r] && lane == 0) a.cnt[r][(size_t)b * M + c] = n;
+            if (a.pad) {
+                const int fill = n > 0 ? first[ci][r] : 0;
+                int32_t *row = a.idx[r] + ((size_t)b * M + c) * a.ns[r];
+                for (int p = n + lane; p < a.ns[r]; p += 32) row[p] = fill;
+            }
+        }
+    }
+}
+
+template <int NR>
+static int bq_launch(const BqArgs &a, int B, cudaStream_t st) {
+    // fewer centres per warp when the grid would not fill the GPU
+    const size_t smem = (size_t)2 * BQ_TILE * 4 * sizeof(float);
+    long ctas8 = (long)div_up(a.M, 8 * BQ_WARPS) * B;
+    if (ctas8 >= 148) {
+        auto k = ball_query_kernel<NR, 8>;
+        DCLR_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<dim3(div_up(a.M, 8 * BQ_WARPS), B), BQ_WARPS * 32, smem, st>>>(a);
+    } else {
+        auto k = ball_query_kernel<NR, 2>;
+        DCLR_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<dim3(div_up(a.M, 2 * BQ_WARPS), B), BQ_WARPS * 32, smem, st>>>(a);
+    }
+    DCLR_LAUNCH_CHECK("ball_query_kernel");
+    return DCLR_OK;
+}
+
+int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
+                      const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad,
+                      cudaStream_t st) {
+    BqArgs a;
+    a.new_xyz = new_xyz; a.pts = pts; a.stride = stride; a.N = N; a.M = M; a.pad = pad;
+    for (int r = 0; r < 2; ++r) {
+        int rr = r < nr ? r : 0;
+        a.r2[r] = radii[rr] * radii[rr];            // float radius2 = radius * radius  (ball_query_gpu.cu:23)
+        a.ns[r] = ns[rr]; a.idx[r] = idx[rr]; a.cnt[r] = cnt ? cnt[rr] : nullptr;
+    }
+    return nr == 2 ? bq_launch<2>(a, B, st) : bq_launch<1>(a, B, st);
+}
+
+// ------------------------------------------------------------------ kNN
+constexpr int KNN_WARPS = 8;
+constexpr int KNN_KPL = 32;                 // keys per lane per tile
+constexpr int KNN_TILE = 32 * KNN_KPL;      // 1024 candidates per tile
+constexpr int KNN_MAXK = 128;
+
+__device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
+    uint32_t hi = (uint32_t)(v >> 32);
+    uint32_t mhi = __reduce_min_sync(0xffffffffu, hi);
+    uint32_t lo = (hi == mhi) ? (uint32_t)v : 0xffffffffu;
+    uint32_t mlo = __reduce_min_sync(0xffffffffu, lo);
+    return ((uint64_t)mhi << 32) | mlo;
+}
+
+__global__ void __launch_bounds__(KNN_WARPS * 32)
+knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
+           int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local) {
+    __shared__ float s_c[KNN_TILE * 3];
+    __shared__ uint64_t s_win[KNN_WARPS][KNN_MAXK];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y;
+    const int q = blockIdx.x * KNN_WARPS + warp;
+    const bool active = q < Ny;
+    const float *xb = x + (size_t)b * Nx * 3;
+    const size_t gy = (size_t)b * Ny + (active ? q : 0);
+    const float qx = __ldg(y + gy * 3), qy = __ldg(y + gy * 3 + 1), qz = __ldg(y + gy * 3 + 2);
+    const uint64_t KMAX = ~0ull;
+    const int ntiles = (Nx + KNN_TILE - 1) / KNN_TILE;
+
+    for (int t = 0; t < ntiles; ++t) {
+        const int base = t * KNN_TILE;
+        const int tile_cnt = min(KNN_TILE, Nx - base);
+        __syncthreads();
+        for (int e = tid; e < tile_cnt * 3; e += KNN_WARPS * 32) s_c[e] = __ldg(xb + (size_t)base * 3 + e);
+        __syncthreads();
+        if (!active) continue;
+        uint64_t keys[KNN_KPL + 4];
+#pragma unroll
+        for (int i = 0; i < KNN_KPL; ++i) {
+            const int j = i * 32 + lane;
+            uint64_t key = KMAX;
+            if (j < tile_cnt) {
+                // torch-cluster: tmp_dist += (x - y)^2 per dimension, x = candidate, y = query
+                float d = sqdist_tc(s_c[j * 3] - qx, s_c[j * 3 + 1] - qy, s_c[j * 3 + 2] - qz);
+                key = ((uint64_t)__float_as_uint(d) << 32) | (uint32_t)(base + j);
+            }
+            keys[i] = key;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {     // winners carried over from earlier tiles
+            const int w = lane + 32 * c;
+            keys[KNN_KPL + c] = (t > 0 && w < k) ? s_win[warp][w] : KMAX;
+        }
+        __syncwarp();
+        uint64_t lmin = KMAX;
+#pragma unroll
+        for (int i = 0; i < KNN_KPL + 4; ++i) lmin = keys[i] < lmin ? keys[i] : lmin;
+        for (int r = 0; r < k; ++r) {
+            const uint64_t win = warp_min_u64(lmin);
+            if (lane == 0) s_win[warp][r] = win;
+            if (lmin == win) {            // exactly one lane (indices are unique)
+                uint64_t nm = KMAX;
+#pragma unroll
+                for (int i = 0; i < KNN_KPL + 4; ++i) {
+                    uint64_t v = keys[i];
+                    v = (v == win) ? KMAX : v;
+                    keys[i] = v;
+                    nm = v < nm ? v : nm;
+                }
+                lmin = nm;
+            }
+        }
+        __syncwarp();
+    }
+    if (!active) return;
+    for (int r = lane; r < k; r += 32) {
+        const uint32_t ci = (uint32_t)s_win[warp][r];
+        const size_t o = gy * k + r;
+        if (row_out) row_out[o] = (int64_t)gy;
+        if (col_out) col_out[o] = (int64_t)((size_t)b * Nx + ci);
+        if (col_local) col_local[o] = (int32_t)ci;
+    }
+}
+
+int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
+               int32_t *col_local, cudaStream_t st) {
+    knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+    DCLR_LAUNCH_CHECK("knn_kernel");
+    return DCLR_OK;
+}
+
+}  // namespace dclr
+
+// ------------------------------------------------------------------ C ABI
+extern "C" int dclr_gather(const float *feat, const int32_t *idx, int B, int C, int N, int M, float *out,
+                           void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(feat && idx && out, "dclr_gather: null pointer");
+    DCLR_CHECK_ARG(B >= 0 && C >= 1 && N >= 1 && M >= 0 && C <= 65535 && B <= 65535, "dclr_gather: bad shape");
+    if (B == 0 || M == 0) return DCLR_OK;
+    gather_kernel<<<dim3(div_up(M, 256), C, B), 256, 0, (cudaStream_t)stream>>>(feat, idx, C, N, M, out);
+    DCLR_LAUNCH_CHECK("gather_kernel");
+    return DCLR_OK;
+}
+
+extern "C" int dclr_group(const float *feat, const int32_t *idx, int B, int C, int N, int M, int nsample, float *out,
+                          void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(feat && idx && out, "dclr_group: null pointer");
+    DCLR_CHECK_ARG(B >= 0 && C >= 1 && N >= 1 && M >= 0 && nsample >= 0 && C <= 65535 && B <= 65535,
+                   "dclr_group: bad shape");
+    if (B == 0 || M == 0 || nsample == 0) return DCLR_OK;
+    size_t total = (size_t)M * nsample;
+    group_kernel<<<dim3((unsigned)((total + 255) / 256), C, B), 256, 0, (cudaStream_t)stream>>>(feat, idx, C, N, M,
+                                                                                                nsample, out);
+    DCLR_LAUNCH_CHECK("group_kernel");
+    return DCLR_OK;
+}
+
+extern "C" int dclr_ball_query(const float *new_xyz, const float *pts, int pt_stride, int B, int N, int M,
+                               float radius, int nsample, int32_t *idx_out, int32_t *cnt_out, int pad, void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(new_xyz && pts && idx_out, "dclr_ball_query: null pointer");
+    DCLR_CHECK_ARG(pt_stride >= 3 && B >= 0 && N >= 1 && M >= 0 && nsample >= 1 && B <= 65535,
+                   "dclr_ball_query: bad shape");
+    if (B == 0 || M == 0) return DCLR_OK;
+    int32_t *idx[1] = {idx_out};
+    int32_t *cnt[1] = {cnt_out};
+    return ball_query_launch(new_xyz, pts, pt_stride, B, N, M, 1, &radius, &nsample, idx, cnt, pad,
+                             (cudaStream_t)stream);
+}
+
+extern "C" int dclr_knn(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row_out,
+                        int64_t *col_out, void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(x && y && row_out && col_out, "dclr_knn: null pointer");
+    DCLR_CHECK_ARG(B >= 0 && Nx >= 1 && Ny >= 0 && B <= 65535, "dclr_knn: bad shape");
+    DCLR_CHECK_ARG(k >= 1 && k <= Nx && k <= KNN_MAXK, "dclr_knn: need 1 <= k <= min(Nx,%d), got k=%d Nx=%d", KNN_MAXK,
+                   k, Nx);
+    if (B == 0 || Ny == 0) return DCLR_OK;
+    return knn_launch(x, y, B, Nx, Ny, k, row_out, col_out, nullptr, (cudaStream_t)stream);
+}

@@ -1,0 +1,91 @@
+"""BaseModel and ModelInferenceHelper: the inference API of the reference (deepclr/models/base.py:9-136)."""
+import abc
+import warnings
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+
+class BaseModel(nn.Module, metaclass=abc.ABCMeta):
+    """Interface of all registration models."""
+
+    @abc.abstractmethod
+    def get_input_dim(self) -> int:
+        raise NotImplementedError
+
+    @abc.abstractmethod
+    def has_loss(self) -> bool:
+        raise NotImplementedError
+
+    @abc.abstractmethod
+    def get_loss_weights(self) -> Dict:
+        raise NotImplementedError
+
+    @abc.abstractmethod
+    def forward(self, x: torch.Tensor, is_feat: bool = False, m: Optional[torch.Tensor] = None,
+                y: Optional[torch.Tensor] = None, debug: bool = False)\
+            -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[Dict]]:
+        """x: cloud batch [2B,N,C] (templates first) or features if is_feat; returns (y_pred, loss, debug)."""
+        raise NotImplementedError
+
+    @abc.abstractmethod
+    def cloud_features(self, x: torch.Tensor, m: Optional[torch.Tensor] = None) -> torch.Tensor:
+        raise NotImplementedError
+
+
+class ModelInferenceHelper:
+    """Sequential (odometry) and pairwise prediction with the reference's semantics: extra point channels are
+    truncated with a warning, too few raise; sequential mode caches the previous frame's set-abstraction
+    features; clouds of different size are randomly sub-sampled to the smaller one."""
+
+    def __init__(self, model: BaseModel, is_sequential: bool = False):
+        self._model = model
+        self._input_dim = model.get_input_dim()
+        self._model.eval()
+        self._is_sequential = is_sequential
+        self._state: Optional[torch.Tensor] = None
+
+    def has_state(self) -> bool:
+        return self._state is not None
+
+    def reset_state(self) -> None:
+        self._state = None
+
+    def _fit_dim(self, cloud: torch.Tensor, what: str) -> torch.Tensor:
+        if cloud.shape[1] > self._input_dim:
+            warnings.warn(f"Truncate {what} point cloud from dimension {cloud.shape[1]} "
+                          f"to required dimension {self._input_dim}.")
+            return cloud[:, :self._input_dim]
+        if cloud.shape[1] < self._input_dim:
+            raise RuntimeError(f"Wrong point dimension in {what}.")
+        return cloud
+
+    def predict(self, source: torch.Tensor, template: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        source = self._fit_dim(source, 'source')
+        if template is not None:
+            template = self._fit_dim(template, 'template')
+        with torch.no_grad():
+            if self._is_sequential:
+                if template is not None:
+                    raise RuntimeError("Only the source cloud is required for sequential prediction.")
+                feat = self._model.cloud_features(source.unsqueeze(0))[0, ...]
+                previous, self._state = self._state, feat
+                if previous is None:
+                    return None
+                y, _, _ = self._model.forward(self.stack(previous, feat), is_feat=True)
+                return y[0, :]
+            if template is None:
+                raise RuntimeError("Source and template clouds are required for non-sequential prediction.")
+            y, _, _ = self._model.forward(self.stack(template, source), is_feat=False)
+            return y[0, :]
+
+    @staticmethod
+    def stack(template: torch.Tensor, source: torch.Tensor) -> torch.Tensor:
+        """[2, N, C] batch, template first; the larger cloud is randomly reduced to the smaller size."""
+        n = min(template.shape[0], source.shape[0])
+        if source.shape[0] > n:
+            source = source[torch.randperm(source.shape[0])[:n], :]
+        elif template.shape[0] > n:
+            template = template[torch.randperm(template.shape[0])[:n], :]
+        return torch.stack((template, source), 0)

@@ -1,0 +1,134 @@
+/*
+ * deepclr_b200.h -- C ABI of libdeepclr_b200.so (hand-written CUDA for sm_100a).
+ *
+ * Drop-in boundary for the registration forward path of Leedk3/deepclr.  Each entry point names the reference
+ * interface it replaces (paths relative to the reference tree).  Conventions:
+ *   - every pointer is a DEVICE pointer owned by the caller (the reference's wrappers also only borrow data_ptrs:
+ *     extern/Pointnet2.PyTorch/pointnet2/pointnet2_utils.py:25-28,55-57,172-174,218-220);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is enqueued
+ *     asynchronously on it, nothing synchronises, so every call is CUDA-graph capturable;
+ *   - return value: 0 on success, negative DCLR_E_* otherwise; dclr_last_error() gives a thread-local message.
+ *     (The reference prints and exit(-1)s on launch failure: sampling_gpu.cu:39-43.)
+ *   - index dtype int32 for the PointNet++ ops, int64 for kNN (torch-cluster layout);
+ *   - the current CUDA device of the calling thread is used (same as the reference: no device guard).
+ */
+#ifndef DEEPCLR_B200_H
+#define DEEPCLR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DCLR_OK 0
+#define DCLR_E_INVALID (-1)   /* bad argument (shape, null pointer, unsupported size) */
+#define DCLR_E_CUDA (-2)      /* CUDA runtime error at launch */
+#define DCLR_E_UNSUPPORTED (-3)
+
+/* Library identification; also used by the loader to prove the native code is the one running. */
+const char *dclr_version(void);
+const char *dclr_last_error(void);
+
+/*
+ * Farthest point sampling.  Replaces pointnet2_cuda.furthest_point_sampling_wrapper
+ * (src/sampling.cpp:36-46 -> src/sampling_gpu.cu:94-253) and, when new_xyz_out != NULL, the gather_operation that
+ * always follows it (pointnet2_modules.py:32-35 -> sampling_gpu.cu:8-44).
+ *   pts        [B, N, pt_stride] fp32, xyz in the first three floats of each point (pt_stride >= 3)
+ *   idx_out    [B, npoint] int32; idx[.,0] = 0; ties -> lowest point index
+ *   new_xyz_out[B, npoint, 3] fp32 or NULL
+ * The min-distance scratch the reference makes the caller allocate and fill with 1e10 (pointnet2_utils.py:26)
+ * lives in registers here.  npoint > N is allowed (reference test tests/model/test_deepclr.py:10-25).
+ */
+int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int32_t *idx_out, float *new_xyz_out,
+             void *stream);
+
+/* out[b,c,j] = feat[b,c,idx[b,j]].  Replaces pointnet2_cuda.gather_points_wrapper (sampling.cpp:11-20). */
+int dclr_gather(const float *feat, const int32_t *idx, int B, int C, int N, int M, float *out, void *stream);
+
+/*
+ * Ball query.  Replaces pointnet2_cuda.ball_query_wrapper (src/ball_query.cpp:14-25 -> ball_query_gpu.cu:9-67).
+ *   new_xyz [B,M,3], pts [B,N,pt_stride] (xyz first) -> idx_out [B,M,nsample] int32: first nsample points with
+ *   d^2 < radius^2 in ascending index order, remaining slots = first hit, all zeros when the ball is empty
+ *   (the caller-side zero fill of pointnet2_utils.py:218 is done here).  cnt_out [B,M] (nullable) = genuine hits.
+ *   pad = 0 skips the padding (slots >= cnt are left untouched): the fused path's compact form.
+ */
+int dclr_ball_query(const float *new_xyz, const float *pts, int pt_stride, int B, int N, int M, float radius,
+                    int nsample, int32_t *idx_out, int32_t *cnt_out, int pad, void *stream);
+
+/* out[b,c,i,j] = feat[b,c,idx[b,i,j]].  Replaces pointnet2_cuda.group_points_wrapper (group_points.cpp:25-35).
+ * Compatibility/parity only: the fused path never materialises this tensor. */
+int dclr_group(const float *feat, const int32_t *idx, int B, int C, int N, int M, int nsample, float *out,
+               void *stream);
+
+/*
+ * Batched kNN.  Replaces torch_cluster.knn(x, y, k, batch_x, batch_y) as called at deepclr/models/deepclr.py:164-166
+ * (equal-sized, sorted batches).  x [B*Nx,3] candidates, y [B*Ny,3] queries.  row_out/col_out [B*Ny*k] int64:
+ * row = global y row id, col = global x row id, ascending distance, ties -> lower x index.  Needs 0 < k <= min(Nx,128).
+ */
+int dclr_knn(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row_out, int64_t *col_out,
+             void *stream);
+
+/* ---- fused model path --------------------------------------------------------------------------------- */
+
+typedef struct dclr_model dclr_model;   /* opaque; device-resident weights + workspace */
+
+/* Architecture = the `params` block of a reference model_config.yaml (models/kitti_00-10/model_config.yaml). */
+typedef struct {
+    int input_dim;            /* 3 or 4 (xyz [+ 1 feature])                            model_config.yaml:2 */
+    int npoint;               /* set-abstraction samples                               :12-13 */
+    int num_scales;           /* 1 or 2 */
+    float radii[2];           /* :14-16 */
+    int nsamples[2];          /* :17-19 */
+    int sa_mlp[2][3];         /* hidden sizes per scale, e.g. {16,16,32}               :20-26 */
+    int knn_k;                /* :30 */
+    float merge_radius;       /* :31 (<= 0 disables the mask, deepclr.py:220) */
+    int merge_mlp[3];         /* :32-35 */
+    int out_mlp[5];           /* :39-44 */
+    int out_linear[3];        /* :45-48 (first entry == out_mlp[4]) */
+    int label_type;           /* 0 EULER(6) 1 QUAT(7) 2 DUAL_QUAT(8)                   deepclr/data/labels.py:12-24 */
+} dclr_arch;
+
+/*
+ * weights: HOST pointer to all parameters as fp32, concatenated in the reference's state_dict order
+ * (SURVEY.md section 3.3): SA scale0 (W,b)x3, SA scale1 (W,b)x3, merge (W,b)x3, output conv (W,b)x5,
+ * linear (W,b)x2, final (W,b); each W row-major [Cout,Cin].  Copied to the device (synchronously).
+ */
+int dclr_model_create(const dclr_arch *arch, const float *weights, size_t num_floats, dclr_model **out);
+void dclr_model_destroy(dclr_model *m);
+/* numerics: 0 = fp32 SIMT everywhere (fp32-faithful), 1 = bf16 tcgen05 tensor-core MLPs (fp32 accumulate) */
+int dclr_model_set_numerics(dclr_model *m, int mode);
+
+/*
+ * Set abstraction (deepclr.py:510-521 -> :88-94 -> pointnet2_modules.py:19-55).
+ *   x [num_clouds, N, input_dim] fp32 -> feat_out [num_clouds, 3+F, npoint] fp32 (reference layout, xyz rows first).
+ */
+int dclr_cloud_features(dclr_model *m, const float *x, int num_clouds, int N, float *feat_out, void *stream);
+
+/*
+ * Merge + output on precomputed features (DeepCLR.forward(is_feat=True), deepclr.py:492-496; used by the sequential
+ * ModelInferenceHelper, deepclr/models/base.py:97-112).  feat [2B, 3+F, npoint] templates first -> y_out [B, label_dim].
+ * motion_out (nullable) [B, 3+merge_mlp[2], npoint] = MotionEmbedding output.
+ */
+int dclr_forward_features(dclr_model *m, const float *feat, int B, float *y_out, float *motion_out, void *stream);
+
+/*
+ * Whole forward (DeepCLR.forward, deepclr.py:488-508): x [2B, N, input_dim] templates first -> y_out [B, label_dim].
+ * feat_out (nullable) as in dclr_cloud_features; motion_out (nullable) as above.
+ */
+int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, float *y_out, float *feat_out,
+                       float *motion_out, void *stream);
+
+/* Number of kernels the last dclr_forward_* / dclr_cloud_features call on this model enqueued. */
+int dclr_model_last_launches(const dclr_model *m);
+/* Debug/parity taps of the last forward: copies `nbytes` of a workspace array into dst (device) on `stream`.
+ * which: 0 fps idx [2B,npoint] i32; 1 ball cnt scale0 [2B,npoint] i32; 2 ball cnt scale1; 3 knn col [B*npoint*k] i32
+ * (source index local to the pair); 4 ball idx scale0 (compact, only the first cnt slots of a row are defined)
+ * [2B,npoint,ns0] i32; 5 ball idx scale1. */
+int dclr_model_debug_copy(const dclr_model *m, int which, void *dst, size_t nbytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEEPCLR_B200_H */
