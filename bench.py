@@ -1,0 +1,309 @@
+"""bench.py -- registered pairs/s of the DeepCLR forward path (KITTI-shaped 16384-point pairs) on N B200s.
+
+  python bench.py [--gpus N --steps K --warmup W]            this repo's sm_100a path (C ABI, libdeepclr_b200.so)
+  python bench.py --impl reference [...]                     the reference algorithm on the host cores (CPU oracle)
+
+One "step" = one forward over one batch of `--pairs` synthetic KITTI-shaped pairs per GPU (weak scaling: pairs are
+independent, every rank works on its own batch, no collective on the data path).  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'registered pairs/sec (KITTI 16k pts)'
+FLOP_PER_PAIR = {'kitti': 10.0849e9, 'modelnet': 4.3844e9}     # dense-equivalent MLP work, SURVEY.md section 8
+ROTATE = 4                                                     # distinct resident input batches cycled per step
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='native', choices=['native', 'reference'])
+    ap.add_argument('--pairs', type=int, default=64, help='pairs per GPU per step')
+    ap.add_argument('--points', type=int, default=16384)
+    ap.add_argument('--kind', default='kitti', choices=['kitti', 'modelnet'])
+    ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'bf16'), choices=['fp32', 'bf16'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--cpu-pairs', type=int, default=8, help='pairs of the bounded CPU sample')
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d['hbm_gbs']), tf=float(d['bf16_tflops_sustained']), src='measured')
+    return dict(hbm=6650.0, tf=1400.0, src='fallback')
+
+
+def build_model_and_cfg(kind):
+    """Random-init DeepCLR (torch.manual_seed(0)) from the reference-shaped model config."""
+    import torch
+    import yaml
+    from deepclr_b200.config import load_model_config
+    from deepclr_b200.models import build_model
+    path = os.path.join(ROOT, 'configs', f'{"kitti" if kind == "kitti" else "modelnet40"}_model.yaml')
+    cfg = load_model_config(path, '')
+    torch.manual_seed(0)
+    model = build_model(cfg).eval()
+    return model, yaml.safe_load(open(path))
+
+
+def make_batches(kind, pairs, points, count, seed0):
+    """`count` distinct [2*pairs, points, C] batches.  Generating 16k-point scans is slow in numpy, so a batch is
+    assembled from a pool of seeded pairs; every batch is a different selection (no two identical inputs in a row)."""
+    from deepclr_b200 import synth
+    pool_n = min(pairs, 16)
+    gen = synth.kitti_pair if kind == 'kitti' else synth.modelnet_pair
+    pool = [gen(seed0 + i, points)[:2] for i in range(pool_n)]
+    rng = np.random.default_rng(seed0)
+    out = []
+    for _ in range(count):
+        sel = rng.integers(0, pool_n, pairs)
+        # rigidly shift every copy a little so the duplicates are not bit-identical clouds
+        t = np.stack([pool[i][0] for i in sel])
+        s = np.stack([pool[i][1] for i in sel])
+        off = rng.uniform(-0.05, 0.05, (pairs, 1, 3)).astype(np.float32)
+        t[:, :, :3] += off
+        s[:, :, :3] += off
+        out.append(np.ascontiguousarray(np.concatenate([t, s], 0)))
+    return out
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop.is_set():
+            try:
+                o = subprocess.run(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                    '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                f = [v.strip() for v in o.strip().split(',')]
+                if len(f) >= 7:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def finish(self):
+        self._stop.set()
+        self.join(6)
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for j, n in enumerate(names) if any(r[3 + j].lower().startswith('active') for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.rows[0][1]), 'reasons': reasons,
+                'samples': len(self.rows)}
+
+
+def cpu_oracle_pairs_per_s(kind, points, n_pairs, warm=1):
+    """The reference algorithm on the host cores: oracle/model_oracle.py (torch CPU fp32 dense layers with all host
+    threads + OpenMP C restatements of the reference point kernels).  Bounded sample of the bench workload."""
+    import torch
+    from oracle import model_oracle, ops
+    model, cfg = build_model_and_cfg(kind)
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    xs = make_batches(kind, 1, points, min(n_pairs, 4), 1234)
+    for i in range(warm):
+        model_oracle.forward(sd, cfg, torch.from_numpy(xs[0]))
+    t0 = time.perf_counter()
+    for i in range(n_pairs):
+        model_oracle.forward(sd, cfg, torch.from_numpy(xs[i % len(xs)]))
+    dt = time.perf_counter() - t0
+    cores = max(torch.get_num_threads(), ops.num_threads())
+    return n_pairs / dt, cores, dt
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (the oracle port; the reference's own Python
+    needs /root/reference and third-party wheels that do not exist on the GPU box).  Rank 0 only."""
+    if rank != 0:
+        return
+    per_step = max(1, args.cpu_pairs // 4)
+    import torch
+    from oracle import model_oracle, ops
+    model, cfg = build_model_and_cfg(args.kind)
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    xs = make_batches(args.kind, 1, args.points, 4, 1234)
+    step = lambda i: [model_oracle.forward(sd, cfg, torch.from_numpy(xs[(i + j) % 4])) for j in range(per_step)]
+    for i in range(args.warmup):
+        step(i)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step(i)
+    dt = time.perf_counter() - t0
+    value = per_step * args.steps / dt
+    cores = max(torch.get_num_threads(), ops.num_threads())
+    sample = f'{per_step} pair(s) of {args.points} points per step, batch 1 forwards'
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'{args.kind}_{args.points}pts_batch{args.pairs}_per_gpu', 'sample': sample},
+            'cpu_baseline': {'value': value, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_native(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), 'bench.py (native arm) needs a CUDA device: there is no CPU path'
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    peaks = load_peaks()
+    model, _ = build_model_and_cfg(args.kind)
+    model = model.to(dev)
+    model.numerics = args.numerics
+    host = [torch.from_numpy(b).pin_memory() for b in make_batches(args.kind, args.pairs, args.points, ROTATE,
+                                                                   1234 + 1000 * rank)]
+    resident = [h.to(dev) for h in host]
+    B = args.pairs
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """K steps between a barrier + synchronize on both sides, CUDA events on the launching stream; ms, max over ranks."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident arm: inputs already in HBM
+    def step_resident(i):
+        with torch.no_grad():
+            return model(resident[i % ROTATE])[0]
+
+    for i in range(args.warmup):
+        step_resident(i)
+    native = model._native
+    native.set_timing(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms = timed(step_resident, args.steps)
+    clocks = sampler.finish() if rank == 0 else None
+    stage_ms, calls = native.collect_timing()
+    native.set_timing(False)
+    launches = native.last_launches() * args.steps
+    value = world * B * args.steps / (ms * 1e-3)
+
+    # ---- end-to-end arm: public API with host buffers, H2D of the inputs and D2H of the poses inside the timed region
+    dbuf = torch.empty_like(resident[0])
+    ybuf = torch.empty((B, 8), dtype=torch.float32).pin_memory()
+
+    def step_e2e(i):
+        dbuf.copy_(host[i % ROTATE], non_blocking=True)
+        with torch.no_grad():
+            y = model(dbuf)[0]
+        ybuf[:, :y.shape[1]].copy_(y, non_blocking=True)
+
+    for i in range(max(3, args.warmup // 2)):
+        step_e2e(i)
+    ms_e2e = timed(step_e2e, args.steps)
+    e2e = {'value': world * B * args.steps / (ms_e2e * 1e-3), 'unit': 'pairs/s',
+           'h2d_bytes_per_step': host[0].numel() * 4, 'd2h_bytes_per_step': B * 8 * 4,
+           'ms_per_step': ms_e2e / args.steps}
+
+    # ---- batch-1 latency (BASELINE.json configs[1]): p50 of single-pair forwards, CUDA events per call
+    lat = []
+    one = [r[[0, B]].contiguous() for r in resident]
+    with torch.no_grad():
+        for i in range(10):
+            model(one[i % ROTATE])
+        for i in range(50):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            model(one[i % ROTATE])
+            b.record()
+            b.synchronize()
+            lat.append(a.elapsed_time(b))
+    lat.sort()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant stage (largest share of the step, timed live with CUDA events on the launch stream)
+    per_call = {k: v / max(calls, 1) for k, v in stage_ms.items()}
+    top = max(per_call, key=per_call.get)
+    flop_stage = {'flow_embed_head': (2700.1e6 + 2149.1e6) if args.kind == 'kitti' else (2025.1e6 + 1074.5e6),
+                  'sa_mlp_maxpool': 5234.4e6 if args.kind == 'kitti' else 1283.4e6}
+    C = 4 if args.kind == 'kitti' else 3
+    M, ns = (1024, (512, 1024)) if args.kind == 'kitti' else (512, (256, 512))
+    G, N = 2 * B, args.points
+    bytes_stage = {'fps': G * (4 * C * N + 4 * M + 12 * M),
+                   'ball_query': G * (4 * C * N + 12 * M + 4 * M * sum(ns)),
+                   'knn': B * (12 * 2 * M + 4 * M * (20 if args.kind == 'kitti' else 30))}
+    if top in flop_stage:
+        ach = B * flop_stage[top] / (per_call[top] * 1e-3) / 1e12
+        roof = {'bound': 'tensor', 'achieved': ach, 'peak': peaks['tf'], 'unit': 'TFLOP/s', 'frac': ach / peaks['tf']}
+    else:
+        ach = bytes_stage.get(top, 0) / (per_call[top] * 1e-3) / 1e9
+        roof = {'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': ach / peaks['hbm']}
+    roof.update({'kernel': top, 'traffic': None, 'peak_source': peaks['src'], 'ms_per_launch': per_call[top],
+                 'share_of_step': per_call[top] / (ms / args.steps)})
+
+    line = {'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'bf16' if args.numerics == 'bf16' else 'f32', 'data': 'synthetic',
+            'config': {'workload': f'{args.kind}_{args.points}pts_batch{B}_per_gpu', 'pairs_per_gpu_per_step': B,
+                       'points_per_cloud': N, 'numerics': args.numerics, 'parallelism': f'dp{world} (independent pairs)',
+                       'l2': f'{ROTATE} distinct resident input batches cycled + >126 MB of per-step workspace traffic'},
+            'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof,
+            'stage_ms': per_call,
+            'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat)},
+            'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
+    if not args.no_cpu_baseline:
+        v, cores, dt = cpu_oracle_pairs_per_s(args.kind, args.points, args.cpu_pairs)
+        line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
+                                'sample': f'{args.cpu_pairs} batch-1 forwards of {N}-point pairs ({dt:.1f} s)'}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local_rank = int(os.environ.get('LOCAL_RANK', 0))
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+    else:
+        run_native(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

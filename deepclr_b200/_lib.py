@@ -38,6 +38,10 @@ _SIGNATURES = {
     'dclr_forward_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_forward_pairs': (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     'dclr_model_last_launches': (c_int, [c_void_p]),
+    'dclr_model_set_timing': (c_int, [c_void_p, c_int]),
+    'dclr_model_stage_count': (c_int, []),
+    'dclr_model_stage_name': (ctypes.c_char_p, [c_int]),
+    'dclr_model_collect_timing': (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int)]),
     'dclr_model_debug_copy': (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
 }
 EXPORTS = tuple(_SIGNATURES)

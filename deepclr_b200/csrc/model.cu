@@ -24,6 +24,12 @@ struct dclr_model {
     float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
     uint8_t *mask;
     dclr::TcModel *tc = nullptr;     // bf16 tensor-core path (mlp_tc.cu)
+    // optional per-stage CUDA-event timing (dclr_model_set_timing): ring of calls x (stages + 1) events
+    bool timing = false;
+    cudaEvent_t *ev = nullptr;
+    int ev_calls = 0;                // calls recorded since the last collect (may exceed the ring)
+    int ev_cur = 0;                  // slot of the call being recorded
+    uint32_t ev_mask[64] = {0};      // stages recorded per ring slot
 };
 
 namespace dclr {
@@ -84,6 +90,32 @@ static int ensure_ws(dclr_model *m, int G, int N, int B) {
     return DCLR_OK;
 }
 
+// stages a forward is split into for timing
+enum { ST_FPS = 0, ST_BALL, ST_SA, ST_KNN, ST_DENSE, ST_TAIL, ST_LAYOUT, ST_COUNT };
+static const char *const kStageNames[ST_COUNT] = {"fps", "ball_query", "sa_mlp_maxpool", "knn",
+                                                  "flow_embed_head", "pose_tail", "layout"};
+constexpr int EV_RING = 64;
+constexpr int EV_PER_CALL = 2 * ST_COUNT;      // begin/end per stage
+
+static void timing_begin_call(dclr_model *m) {
+    if (!m->timing) return;
+    m->ev_cur = m->ev_calls % EV_RING;
+    ++m->ev_calls;
+    m->ev_mask[m->ev_cur] = 0;
+}
+// records begin (which = 0) / end (which = 1) of stage s; a stage hit twice in one call keeps the first begin/last end
+static void timing_mark(dclr_model *m, int s, int which, cudaStream_t st) {
+    if (!m->timing) return;
+    if (which == 0 && (m->ev_mask[m->ev_cur] >> s & 1u)) return;
+    m->ev_mask[m->ev_cur] |= 1u << s;
+    cudaEventRecord(m->ev[(size_t)m->ev_cur * EV_PER_CALL + 2 * s + which], st);
+}
+struct StageScope {
+    dclr_model *m; int s; cudaStream_t st;
+    StageScope(dclr_model *m_, int s_, cudaStream_t st_) : m(m_), s(s_), st(st_) { timing_mark(m, s, 0, st); }
+    ~StageScope() { timing_mark(m, s, 1, st); }
+};
+
 #define DCLR_TRY(expr)            \
     do {                          \
         int rc__ = (expr);        \
@@ -94,9 +126,16 @@ static int ensure_ws(dclr_model *m, int G, int N, int B) {
 // FPS -> ball query (both radii, one pass) -> grouped MLP + max-pool.  pointnet2_modules.py:19-55
 static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cudaStream_t st) {
     const dclr_arch &a = m->arch;
-    DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
-    DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
-                               m->bq_idx, m->bq_cnt, /*pad=*/0, st));
+    {
+        StageScope sc(m, ST_FPS, st);
+        DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+    }
+    {
+        StageScope sc(m, ST_BALL, st);
+        DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
+                                   m->bq_idx, m->bq_cnt, /*pad=*/0, st));
+    }
+    StageScope sc(m, ST_SA, st);
     SaArgs s;
     s.x = x; s.new_xyz = m->new_xyz; s.N = N; s.M = a.npoint; s.ld_out = m->F; s.nscales = a.num_scales;
     s.out = m->sa_feat;
@@ -115,7 +154,11 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     const size_t BM = (size_t)B * M, R = BM * k;
     const int ldm = (int)align_up(3 + a.merge_mlp[2], 4);
     // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
-    DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, st));
+    {
+        StageScope sc(m, ST_KNN, st);
+        DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, st));
+    }
+    timing_mark(m, ST_DENSE, 0, st);
     if (m->numerics == 1) {
         int rc = tc_merge_output(m->tc, m->new_xyz, m->sa_feat, m->knn_col, B, M, m->motion, ldm, m->pooled, st,
                                  &m->last_launches);
@@ -143,6 +186,8 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
         }
         DCLR_TRY(rowmax_launch(in, ldin, B, M, a.out_mlp[4], m->pooled, st));
     }
+    timing_mark(m, ST_DENSE, 1, st);
+    timing_mark(m, ST_TAIL, 0, st);
     // fully connected tail: helper.py:97-123 (ReLU after both), final nn.Linear, activation deepclr.py:275-282
     DCLR_TRY(linear_f32_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
                                a.out_linear[1], a.out_linear[0], 1, st));
@@ -151,8 +196,11 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     DCLR_TRY(linear_f32_launch(m->t2, a.out_linear[2], m->fin.W, m->fin.b, y_out, m->label_dim, B, m->label_dim,
                                a.out_linear[2], 0, st));
     DCLR_TRY(pose_activation_launch(y_out, B, m->label_dim, a.label_type, st));
-    if (motion_out)
+    timing_mark(m, ST_TAIL, 1, st);
+    if (motion_out) {
+        StageScope sc(m, ST_LAYOUT, st);
         DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, ldm, 0, B, M, a.merge_mlp[2], motion_out, st));
+    }
     return DCLR_OK;
 }
 
@@ -223,6 +271,10 @@ extern "C" int dclr_model_create(const dclr_arch *arch, const float *weights, si
 extern "C" void dclr_model_destroy(dclr_model *m) {
     if (!m) return;
     if (m->tc) tc_destroy(m->tc);
+    if (m->ev) {
+        for (int i = 0; i < EV_RING * EV_PER_CALL; ++i) cudaEventDestroy(m->ev[i]);
+        delete[] m->ev;
+    }
     if (m->ws) cudaFree(m->ws);
     if (m->d_w) cudaFree(m->d_w);
     delete m;
@@ -248,10 +300,12 @@ extern "C" int dclr_cloud_features(dclr_model *m, const float *x, int num_clouds
     DCLR_CHECK_ARG(num_clouds >= 1 && N >= 1, "dclr_cloud_features: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     m->last_launches = 0;
+    timing_begin_call(m);
     int rc = ensure_ws(m, num_clouds, N, (num_clouds + 1) / 2);
     if (rc != DCLR_OK) return rc;
     rc = run_set_abstraction(m, x, num_clouds, N, st);
     if (rc != DCLR_OK) return rc;
+    StageScope sc(m, ST_LAYOUT, st);
     DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->sa_feat, m->F, 0, num_clouds, m->arch.npoint, m->F, feat_out, st));
     return DCLR_OK;
 }
@@ -263,9 +317,13 @@ extern "C" int dclr_forward_features(dclr_model *m, const float *feat, int B, fl
     DCLR_CHECK_ARG(m->arch.knn_k <= m->arch.npoint, "knn k=%d exceeds npoint=%d", m->arch.knn_k, m->arch.npoint);
     cudaStream_t st = (cudaStream_t)stream;
     m->last_launches = 0;
+    timing_begin_call(m);
     int rc = ensure_ws(m, 2 * B, 1, B);
     if (rc != DCLR_OK) return rc;
-    DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, st));
+    {
+        StageScope sc(m, ST_LAYOUT, st);
+        DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, st));
+    }
     return run_merge_output(m, B, y_out, motion_out, st);
 }
 
@@ -276,16 +334,53 @@ extern "C" int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, f
     DCLR_CHECK_ARG(m->arch.knn_k <= m->arch.npoint, "knn k=%d exceeds npoint=%d", m->arch.knn_k, m->arch.npoint);
     cudaStream_t st = (cudaStream_t)stream;
     m->last_launches = 0;
+    timing_begin_call(m);
     int rc = ensure_ws(m, 2 * B, N, B);
     if (rc != DCLR_OK) return rc;
     rc = run_set_abstraction(m, x, 2 * B, N, st);
     if (rc != DCLR_OK) return rc;
-    if (feat_out)
+    if (feat_out) {
+        StageScope sc(m, ST_LAYOUT, st);
         DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->sa_feat, m->F, 0, 2 * B, m->arch.npoint, m->F, feat_out, st));
+    }
     return run_merge_output(m, B, y_out, motion_out, st);
 }
 
 extern "C" int dclr_model_last_launches(const dclr_model *m) { return m ? m->last_launches : 0; }
+
+extern "C" int dclr_model_set_timing(dclr_model *m, int on) {
+    DCLR_CHECK_ARG(m, "null model");
+    if (on && !m->ev) {
+        m->ev = new (std::nothrow) cudaEvent_t[(size_t)EV_RING * EV_PER_CALL];
+        DCLR_CHECK_ARG(m->ev, "out of host memory");
+        for (int i = 0; i < EV_RING * EV_PER_CALL; ++i) DCLR_CUDA(cudaEventCreate(&m->ev[i]));
+    }
+    m->timing = on != 0;
+    m->ev_calls = 0;
+    return DCLR_OK;
+}
+
+extern "C" int dclr_model_stage_count(void) { return ST_COUNT; }
+extern "C" const char *dclr_model_stage_name(int s) { return (s >= 0 && s < ST_COUNT) ? kStageNames[s] : ""; }
+
+extern "C" int dclr_model_collect_timing(dclr_model *m, float *stage_ms_sum, int *calls_out) {
+    DCLR_CHECK_ARG(m && stage_ms_sum && calls_out, "dclr_model_collect_timing: null pointer");
+    DCLR_CHECK_ARG(m->ev, "dclr_model_collect_timing: timing was never enabled");
+    for (int s = 0; s < ST_COUNT; ++s) stage_ms_sum[s] = 0.f;
+    const int n = m->ev_calls < EV_RING ? m->ev_calls : EV_RING;
+    for (int c = 0; c < n; ++c)
+        for (int s = 0; s < ST_COUNT; ++s) {
+            if (!(m->ev_mask[c] >> s & 1u)) continue;
+            cudaEvent_t e0 = m->ev[(size_t)c * EV_PER_CALL + 2 * s], e1 = m->ev[(size_t)c * EV_PER_CALL + 2 * s + 1];
+            DCLR_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            DCLR_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            stage_ms_sum[s] += ms;
+        }
+    *calls_out = n;
+    m->ev_calls = 0;
+    return DCLR_OK;
+}
 
 extern "C" int dclr_model_debug_copy(const dclr_model *m, int which, void *dst, size_t nbytes, void *stream) {
     DCLR_CHECK_ARG(m && m->ws && dst, "dclr_model_debug_copy: no workspace yet or null dst");

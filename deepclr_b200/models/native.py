@@ -106,6 +106,19 @@ class NativeModel:
     def last_launches(self) -> int:
         return int(_lib.lib().dclr_model_last_launches(self._handle))
 
+    def set_timing(self, on: bool) -> None:
+        _lib.check(_lib.lib().dclr_model_set_timing(self._handle, int(on)), 'dclr_model_set_timing')
+
+    def collect_timing(self):
+        """-> ({stage: summed ms}, calls) over the forwards recorded since the last collect (at most 64)."""
+        n = _lib.lib().dclr_model_stage_count()
+        buf = (ctypes.c_float * n)()
+        calls = ctypes.c_int()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dclr_model_collect_timing(self._handle, buf, ctypes.byref(calls)),
+                       'dclr_model_collect_timing')
+        return {_lib.lib().dclr_model_stage_name(i).decode(): float(buf[i]) for i in range(n)}, calls.value
+
     def debug_tensor(self, which: int, shape, dtype=torch.int32) -> torch.Tensor:
         """Copy of a workspace tap of the last forward (include/deepclr_b200.h: dclr_model_debug_copy)."""
         out = torch.empty(shape, dtype=dtype, device=self.device)

@@ -122,6 +122,17 @@ int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, float *y_out
 
 /* Number of kernels the last dclr_forward_* / dclr_cloud_features call on this model enqueued. */
 int dclr_model_last_launches(const dclr_model *m);
+/*
+ * Per-stage device timing with CUDA events recorded on the caller's stream (the reference times with an event pair
+ * around predict: scripts/timing.py:32-47; this splits that interval by kernel stage).  When on, every
+ * dclr_cloud_features / dclr_forward_* call records begin/end events per stage into a ring of the last 64 calls.
+ * dclr_model_collect_timing synchronises on them, writes the per-stage sum of milliseconds over the recorded calls
+ * into stage_ms_sum[dclr_model_stage_count()] and the number of calls summed into *calls_out, then resets the ring.
+ */
+int dclr_model_set_timing(dclr_model *m, int on);
+int dclr_model_stage_count(void);
+const char *dclr_model_stage_name(int stage);
+int dclr_model_collect_timing(dclr_model *m, float *stage_ms_sum, int *calls_out);
 /* Debug/parity taps of the last forward: copies `nbytes` of a workspace array into dst (device) on `stream`.
  * which: 0 fps idx [2B,npoint] i32; 1 ball cnt scale0 [2B,npoint] i32; 2 ball cnt scale1; 3 knn col [B*npoint*k] i32
  * (source index local to the pair); 4 ball idx scale0 (compact, only the first cnt slots of a row are defined)
