@@ -34,7 +34,7 @@ def parse_args():
     ap.add_argument('--pairs', type=int, default=64, help='pairs per GPU per step')
     ap.add_argument('--points', type=int, default=16384)
     ap.add_argument('--kind', default='kitti', choices=['kitti', 'modelnet'])
-    ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'bf16'), choices=['fp32', 'bf16'])
+    ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'fp16'), choices=['fp32', 'fp16', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--cpu-pairs', type=int, default=8, help='pairs of the bounded CPU sample')
     return ap.parse_args()
@@ -258,7 +258,8 @@ def run_native(args, rank, world, local_rank):
     # ---- roofline of the dominant stage (largest share of the step, timed live with CUDA events on the launch stream)
     per_call = {k: v / max(calls, 1) for k, v in stage_ms.items()}
     top = max(per_call, key=per_call.get)
-    flop_stage = {'flow_embed_head': (2700.1e6 + 2149.1e6) if args.kind == 'kitti' else (2025.1e6 + 1074.5e6),
+    flop_stage = {'flow_embed': 2700.1e6 if args.kind == 'kitti' else 2025.1e6,
+                  'pose_head_conv': 2149.1e6 if args.kind == 'kitti' else 1074.5e6,
                   'sa_mlp_maxpool': 5234.4e6 if args.kind == 'kitti' else 1283.4e6}
     C = 4 if args.kind == 'kitti' else 3
     M, ns = (1024, (512, 1024)) if args.kind == 'kitti' else (512, (256, 512))
@@ -277,7 +278,7 @@ def run_native(args, rank, world, local_rank):
 
     line = {'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
-            'vs_baseline': None, 'dtype': 'bf16' if args.numerics == 'bf16' else 'f32', 'data': 'synthetic',
+            'vs_baseline': None, 'dtype': {'bf16': 'bf16', 'fp16': 'f16', 'fp32': 'f32'}[args.numerics], 'data': 'synthetic',
             'config': {'workload': f'{args.kind}_{args.points}pts_batch{B}_per_gpu', 'pairs_per_gpu_per_step': B,
                        'points_per_cloud': N, 'numerics': args.numerics, 'parallelism': f'dp{world} (independent pairs)',
                        'l2': f'{ROTATE} distinct resident input batches cycled + >126 MB of per-step workspace traffic'},

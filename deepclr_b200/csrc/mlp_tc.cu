@@ -1,13 +1,686 @@
-// placeholder until the tcgen05 kernels land
+// 16-bit tcgen05/TMEM path for the two dense stacks of the forward:
+//   flow_tc_kernel : kNN-gathered rows [f_tmpl | f_src | dp] -> 3 x (linear + bias + ReLU) -> radius mask -> max over k
+//                    (reference deepclr/models/deepclr.py:201-231; rows are built in shared memory, never in HBM)
+//   head_tc_kernel : [motion feat | xyz] -> 5 x (linear + bias + ReLU) -> max over the n points   (deepclr.py:284-287)
+// Operands are bf16 (or fp16) in the canonical no-swizzle K-major UMMA layout, accumulation is fp32 in TMEM.
+//
+// Shared-memory operand layout (both activations and weights): an [R rows x K] tile is stored as K/8 "chunks", each
+// chunk holding 8 consecutive K-elements (16 bytes) of every row, rows consecutive:
+//     byte offset(r, k) = (k / 8) * (R * 16) + r * 16 + (k % 8) * 2
+// i.e. 8x8 core matrices of 128 contiguous bytes, SBO (next 8-row group) = 128 B, LBO (next K chunk) = R * 16 B.
+// An epilogue thread that owns row r therefore writes one 16-byte vector per chunk and a warp writes 512 contiguous
+// bytes: conflict free.  Weights are pre-packed into exactly this image at model creation so that a weight tile is
+// one contiguous cp.async.bulk (TMA engine) transfer.
+//
+// Hidden layers compute D[rows, out] = X[rows, K] * W[out, K]^T (A = activations, thread <-> row in the epilogue).
+// The LAST layer of each stack is computed transposed, D^T[out, rows] = W * X^T (A = weights): TMEM lanes are output
+// channels and TMEM columns are rows, so the max over the k neighbours / over the points is a per-thread reduction
+// over registers -- no shuffles, no shared memory.  Because both operands use the same K-major tile image, swapping
+// the roles costs nothing.
 #include "common.cuh"
+#include "kernels.cuh"
 #include "mlp_tc.cuh"
+#include "ptx.cuh"
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <new>
+#include <vector>
+#include <algorithm>
+
 namespace dclr {
-int tc_create(const TcLayerSpec *, int, int, float, TcModel **) {
-    return fail(DCLR_E_UNSUPPORTED, "tensor-core path not built yet");
+
+constexpr int TC_ROWS = 128;          // rows (UMMA M or N) of every activation tile
+constexpr int TC_LBO = TC_ROWS * 16;  // bytes between K chunks of a 128-row tile
+
+// ---------------------------------------------------------------- descriptors
+// Instruction descriptor for tcgen05.mma.kind::f16 (cute::UMMA::InstrDescriptor): c_format[4,6)=1 (f32),
+// a_format[7,10) / b_format[10,13) = 0 f16 | 1 bf16, a_major bit15 = b_major bit16 = 0 (K-major), n_dim[17,23) = N>>3,
+// m_dim[24,29) = M>>4.
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int is_bf16) {
+    return (1u << 4) | ((uint32_t)is_bf16 << 7) | ((uint32_t)is_bf16 << 10) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
 }
-void tc_destroy(TcModel *) {}
-int tc_merge_output(TcModel *, const float *, const float *, const int32_t *, int, int, float *, int, float *,
-                    cudaStream_t, int *) {
-    return fail(DCLR_E_UNSUPPORTED, "tensor-core path not built yet");
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor), SWIZZLE_NONE, K-major: start>>4 in [0,14),
+// LBO>>4 in [16,30), SBO>>4 in [32,46), version=1 in [46,48).
+__device__ __forceinline__ uint64_t make_sdesc(uint32_t smem_addr, uint32_t lbo_bytes) {
+    return (uint64_t)((smem_addr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+           ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
 }
+
+template <typename T16> struct Cvt;
+template <> struct Cvt<__nv_bfloat16> {
+    static constexpr int is_bf16 = 1;
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+    static __device__ __forceinline__ uint16_t one(float a) {
+        __nv_bfloat16 v = __float2bfloat16_rn(a);
+        return *reinterpret_cast<uint16_t *>(&v);
+    }
+    static __device__ __forceinline__ float back(uint16_t h) { return __uint_as_float((uint32_t)h << 16); }
+};
+template <> struct Cvt<__half> {
+    static constexpr int is_bf16 = 0;
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        // saturate instead of overflowing to inf
+        a = fminf(fmaxf(a, -65504.f), 65504.f);
+        b = fminf(fmaxf(b, -65504.f), 65504.f);
+        __half2 v = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+    static __device__ __forceinline__ uint16_t one(float a) {
+        a = fminf(fmaxf(a, -65504.f), 65504.f);
+        __half v = __float2half_rn(a);
+        return *reinterpret_cast<uint16_t *>(&v);
+    }
+    static __device__ __forceinline__ float back(uint16_t h) { return __half2float(*reinterpret_cast<__half *>(&h)); }
+};
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// ---------------------------------------------------------------- weight packing (model creation time)
+// dst image of rows [row0, row0+R) x padded K [k0, k0+Kt) of W[out,in] (fp32, row-major) in the chunk layout above.
+// nfeat == 0: plain copy, zero padded.  nfeat > 0: the reference puts the 3 coordinates first (deepclr.py:208-210,228);
+// here the nfeat feature columns come first (16-byte aligned chunks) and are followed by NINE coordinate columns
+//     [w_hi(x,y,z) | w_lo(x,y,z) | w_hi(x,y,z)]   against activations   [c_hi(x,y,z) | c_hi(x,y,z) | c_lo(x,y,z)]
+// (hi = value rounded to 16 bits, lo = rounded remainder), i.e. the coordinate contribution w*c is evaluated as
+// w_hi*c_hi + w_lo*c_hi + w_hi*c_lo with ~16 significant bits: metre-scale coordinates (up to 80 m on LiDAR scans)
+// would otherwise lose centimetres to the 8-bit bf16 mantissa.  The columns live in what is padding anyway.
+template <typename T16>
+__global__ void pack_tile_kernel(const float *__restrict__ W, int out, int in, int nfeat, int row0, int R, int k0,
+                                 int Kt, uint16_t *__restrict__ dst) {
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= R * Kt) return;
+    int kk = e % Kt, r = e / Kt;
+    int kp = k0 + kk, row = row0 + r;
+    uint16_t q = 0;
+    if (row < out) {
+        if (nfeat == 0) {
+            if (kp < in) q = Cvt<T16>::one(W[(size_t)row * in + kp]);
+        } else if (kp < nfeat) {
+            q = Cvt<T16>::one(W[(size_t)row * in + kp + 3]);
+        } else if (kp < nfeat + 9) {
+            const int j = kp - nfeat;
+            const float w = W[(size_t)row * in + j % 3];
+            const uint16_t hi = Cvt<T16>::one(w);
+            q = (j / 3 == 1) ? Cvt<T16>::one(w - Cvt<T16>::back(hi)) : hi;
+        }
+    }
+    dst[(size_t)(kk / 8) * (R * 8) + r * 8 + (kk % 8)] = q;
+}
+
+// the two 16-byte chunks holding a coordinate triple as [hi hi lo] (see pack_tile_kernel)
+template <typename T16>
+__device__ __forceinline__ void store_coord_chunks(uint32_t addr0, uint32_t addr1, float x, float y, float z) {
+    const uint16_t xh = Cvt<T16>::one(x), yh = Cvt<T16>::one(y), zh = Cvt<T16>::one(z);
+    const uint16_t xl = Cvt<T16>::one(x - Cvt<T16>::back(xh)), yl = Cvt<T16>::one(y - Cvt<T16>::back(yh)),
+                   zl = Cvt<T16>::one(z - Cvt<T16>::back(zh));
+    st_shared_v4(addr0, xh | ((uint32_t)yh << 16), zh | ((uint32_t)xh << 16), yh | ((uint32_t)zh << 16),
+                 xl | ((uint32_t)yl << 16));
+    st_shared_v4(addr1, zl, 0u, 0u, 0u);
+}
+
+// ---------------------------------------------------------------- shared epilogue pieces
+// Hidden-layer epilogue of one thread (= one tile row): TMEM accumulators [ncols] -> +bias, ReLU -> 16-bit ->
+// the row's 16-byte vectors of the next layer's A/B operand tile.  taddr already contains the warp's lane offset.
+template <typename T16>
+__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int ncols, const float *__restrict__ bias_s,
+                                                uint32_t act_row_addr) {
+    for (int c0 = 0; c0 < ncols; c0 += 32) {
+        uint32_t v[32];
+        ptx::tmem_ld32(taddr + c0, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t p[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int c = q * 8 + e * 2;
+                float a = fmaxf(__uint_as_float(v[c]) + bias_s[c0 + c], 0.f);
+                float b = fmaxf(__uint_as_float(v[c + 1]) + bias_s[c0 + c + 1], 0.f);
+                p[e] = Cvt<T16>::pack(a, b);
+            }
+            st_shared_v4(act_row_addr + (uint32_t)((c0 >> 3) + q) * TC_LBO, p[0], p[1], p[2], p[3]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- flow embedding
+struct FlowArgs {
+    const float *xyz;       // [2B, n, 3] sampled coordinates, templates first
+    const float *feat;      // [2B, n, F] point-major set-abstraction features
+    const int32_t *nbr;     // [B, n, k] source index (local to the pair) of the k nearest source samples
+    const uint16_t *w;      // packed images: W1 [128 x K0p] | W2 [128 x 128] | W3 [H3 x 128] (128-row blocks)
+    const float *bias;      // b1[128] b2[128] b3[H3]
+    float *out;             // [B*n, H3] motion features (coordinates are kept in xyz)
+    int B, n, k, F, K0p, H3;
+    float radius;
+    int groups_per_tile, tiles_per_pair, num_tiles;
+};
+
+constexpr int FLOW_SLOTS = 2;
+constexpr int FLOW_THREADS = (FLOW_SLOTS * 4 + 1) * 32;
+
+template <typename T16>
+__global__ void __launch_bounds__(FLOW_THREADS, 1)
+flow_tc_kernel(FlowArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int K0p = a.K0p, H3 = a.H3;
+    const uint32_t w1_bytes = 128u * K0p * 2, w2_bytes = 128u * 128 * 2, w3_bytes = (uint32_t)H3 * 128 * 2;
+    const uint32_t act_bytes = 128u * K0p * 2;
+    uint8_t *s_w1 = smem, *s_w2 = s_w1 + w1_bytes, *s_w3 = s_w2 + w2_bytes;
+    uint8_t *s_act = s_w3 + w3_bytes;                                    // FLOW_SLOTS x act_bytes
+    float *s_bias = reinterpret_cast<float *>(s_act + FLOW_SLOTS * act_bytes);   // 256 + H3 floats
+    uint32_t *s_maskw = reinterpret_cast<uint32_t *>(s_bias + 256 + H3);         // [FLOW_SLOTS][4]
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_maskw + FLOW_SLOTS * 4);    // wbar, ready[2], done[2]
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 1 + 2 * FLOW_SLOTS);
+    uint64_t *wbar = s_bar, *ready = s_bar + 1, *done = s_bar + 1 + FLOW_SLOTS;
+
+    if (tid == 0) {
+        ptx::mbar_init(wbar, 1);
+        for (int s = 0; s < FLOW_SLOTS; ++s) {
+            ptx::mbar_init(&ready[s], 128);
+            ptx::mbar_init(&done[s], 1);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == FLOW_SLOTS * 4) ptx::tmem_alloc(s_tmem, 512);
+    for (int e = tid; e < 256 + H3; e += FLOW_THREADS) s_bias[e] = __ldg(a.bias + e);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+    const int tiles_per_iter = gridDim.x * FLOW_SLOTS;
+    constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
+
+    if (warp == FLOW_SLOTS * 4) {
+        // ===================== weight load (once) + MMA issue =====================
+        if (lane == 0) {
+            ptx::mbar_expect_tx(wbar, w1_bytes + w2_bytes + w3_bytes);
+            ptx::bulk_g2s(s_w1, a.w, w1_bytes, wbar);
+            ptx::bulk_g2s(s_w2, reinterpret_cast<const uint8_t *>(a.w) + w1_bytes, w2_bytes, wbar);
+            ptx::bulk_g2s(s_w3, reinterpret_cast<const uint8_t *>(a.w) + w1_bytes + w2_bytes, w3_bytes, wbar);
+            ptx::mbar_wait(wbar, 0);
+        }
+        __syncwarp();
+        const uint32_t w1a = ptx::smem_u32(s_w1), w2a = ptx::smem_u32(s_w2), w3a = ptx::smem_u32(s_w3);
+        uint32_t rphase[FLOW_SLOTS] = {0, 0};
+        for (int t0 = blockIdx.x * FLOW_SLOTS; t0 < a.num_tiles; t0 += tiles_per_iter) {
+            for (int layer = 0; layer < 3; ++layer) {
+                for (int s = 0; s < FLOW_SLOTS; ++s) {
+                    if (t0 + s >= a.num_tiles) continue;
+                    if (lane == 0) {
+                        ptx::mbar_wait(&ready[s], rphase[s] & 1);
+                        ptx::tc_fence_after();
+                        const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
+                        const uint32_t dcol = tmem_base + s * 256;
+                        if (layer == 0) {
+                            for (int ks = 0; ks < K0p / 16; ++ks)
+                                ptx::mma_f16_ss(dcol, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
+                                                make_sdesc(w1a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                        } else if (layer == 1) {
+                            for (int ks = 0; ks < 8; ++ks)
+                                ptx::mma_f16_ss(dcol + 128, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
+                                                make_sdesc(w2a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                        } else {
+                            for (int mb = 0; mb < H3 / 128; ++mb)
+                                for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
+                                    ptx::mma_f16_ss(dcol + mb * 128,
+                                                    make_sdesc(w3a + mb * (128 * 128 * 2) + ks * 2 * TC_LBO, TC_LBO),
+                                                    make_sdesc(act + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                        }
+                        ptx::mma_commit(&done[s]);
+                    }
+                    ++rphase[s];
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===================== row build + epilogues (4 warps per slot) =====================
+        const int s = warp >> 2, q = warp & 3;
+        const int r = q * 32 + lane;                                   // tile row == TMEM lane
+        const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
+        const uint32_t act_row = act + r * 16;
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + s * 256;
+        const int k = a.k, n = a.n, F = a.F, g = a.groups_per_tile;
+        uint32_t dphase = 0;
+        for (int tile = blockIdx.x * FLOW_SLOTS + s; tile < a.num_tiles; tile += tiles_per_iter) {
+            const int b = tile / a.tiles_per_pair;
+            const int p0 = (tile - b * a.tiles_per_pair) * g;
+            // ---- build row r = (point p0 + r / k, neighbour r % k): [f_tmpl | f_src | dp | 0]
+            const int grp = r / k, j = r - grp * k;
+            const int pt = p0 + grp;
+            const bool valid = grp < g && pt < n;
+            bool masked = true;
+            if (valid) {
+                const size_t trow = (size_t)b * n + pt;
+                const int src = __ldg(a.nbr + trow * k + j);
+                const size_t srow = (size_t)(a.B + b) * n + src;
+                const float4 *ft = reinterpret_cast<const float4 *>(a.feat + trow * F);
+                const float4 *fs = reinterpret_cast<const float4 *>(a.feat + srow * F);
+#pragma unroll 4
+                for (int c = 0; c < F / 8; ++c) {
+                    const float4 u0 = __ldg(ft + 2 * c), u1 = __ldg(ft + 2 * c + 1);
+                    const float4 v0 = __ldg(fs + 2 * c), v1 = __ldg(fs + 2 * c + 1);
+                    st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
+                                 Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
+                    st_shared_v4(act_row + (F / 8 + c) * TC_LBO, Cvt<T16>::pack(v0.x, v0.y),
+                                 Cvt<T16>::pack(v0.z, v0.w), Cvt<T16>::pack(v1.x, v1.y), Cvt<T16>::pack(v1.z, v1.w));
+                }
+                const float *pt3 = a.xyz + trow * 3, *ps3 = a.xyz + srow * 3;
+                const float dx = __ldg(ps3) - __ldg(pt3), dy = __ldg(ps3 + 1) - __ldg(pt3 + 1),
+                            dz = __ldg(ps3 + 2) - __ldg(pt3 + 2);
+                store_coord_chunks<T16>(act_row + (2 * F / 8) * TC_LBO, act_row + (2 * F / 8 + 1) * TC_LBO, dx, dy, dz);
+                for (int c = 2 * F / 8 + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                // radius mask in fp32 on the raw displacement (deepclr.py:220-222)
+                masked = a.radius > 0.f && sqrtf(dx * dx + dy * dy + dz * dz) >= a.radius;
+            } else {
+                for (int c = 0; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+            }
+            const uint32_t mw = __ballot_sync(0xffffffffu, masked);
+            if (lane == 0) s_maskw[s * 4 + q] = mw;
+            ptx::fence_proxy_async_smem();
+            ptx::mbar_arrive(&ready[s]);
+            // ---- layer 1 epilogue -> H1 (in place of the rows)
+            ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
+            ptx::tc_fence_after();
+            epilogue_hidden<T16>(tlane, 128, s_bias, act_row);
+            ptx::tc_fence_before();
+            ptx::fence_proxy_async_smem();
+            ptx::mbar_arrive(&ready[s]);
+            // ---- layer 2 epilogue -> H2
+            ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
+            ptx::tc_fence_after();
+            epilogue_hidden<T16>(tlane + 128, 128, s_bias + 128, act_row);
+            ptx::tc_fence_before();
+            ptx::fence_proxy_async_smem();
+            ptx::mbar_arrive(&ready[s]);
+            // ---- layer 3 epilogue (transposed): lane = output channel, columns = tile rows; max over each group
+            ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
+            ptx::tc_fence_after();
+            uint32_t mk[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mk[i] = s_maskw[s * 4 + i];
+            for (int mb = 0; mb < H3 / 128; ++mb) {
+                const int ch = mb * 128 + r;
+                const float bias = s_bias[256 + ch];
+                float cur = -INFINITY;
+                int cnt = 0, og = 0;
+#pragma unroll
+                for (int c0 = 0; c0 < 128; c0 += 32) {
+                    uint32_t v[32];
+                    ptx::tmem_ld32(tlane + mb * 128 + c0, v);
+                    ptx::tmem_ld_wait();
+                    const uint32_t mword = mk[c0 >> 5];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        if (!((mword >> i) & 1u)) cur = fmaxf(cur, __uint_as_float(v[i]));
+                        if (++cnt == k) {
+                            if (og < g && p0 + og < n)
+                                a.out[((size_t)b * n + p0 + og) * H3 + ch] = fmaxf(cur + bias, 0.f);
+                            ++og; cnt = 0; cur = -INFINITY;
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+        }
+    }
+    __syncthreads();
+    if (warp == FLOW_SLOTS * 4) ptx::tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------- output head
+constexpr int HEAD_LAYERS = 5;
+constexpr int HEAD_KT = 64;                      // K elements per streamed weight tile (128 rows x 64 = 16 KB)
+constexpr int HEAD_STAGES = 5;
+constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
+constexpr int HEAD_THREADS = 6 * 32;             // 4 epilogue warps, 1 weight-producer warp, 1 MMA warp
+
+struct HeadArgs {
+    const float *feat;      // [B*n, C0] motion features
+    const float *xyz;       // [B*n, 3] template sample coordinates
+    const uint16_t *w;      // packed weight tiles in (layer, 128-row block, K block) order
+    const float *bias;      // biases of the 5 layers, concatenated
+    float *pooled;          // [B, out[4]] zero-initialised; max over the points
+    int B, n, C0;
+    int Kp[HEAD_LAYERS];    // padded input width per layer (multiple of 16)
+    int out[HEAD_LAYERS];   // output width per layer (multiple of 128)
+    int tiles_per_pair, num_tiles, act_k;        // act_k = widest activation (elements)
+};
+
+template <typename T16>
+__global__ void __launch_bounds__(HEAD_THREADS, 1)
+head_tc_kernel(HeadArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int nbias = 0;
+    for (int l = 0; l < HEAD_LAYERS; ++l) nbias += a.out[l];
+    uint8_t *s_act = smem;                                              // 128 x act_k x 2
+    uint8_t *s_wt = s_act + (size_t)128 * a.act_k * 2;                  // HEAD_STAGES x 16 KB
+    float *s_bias = reinterpret_cast<float *>(s_wt + HEAD_STAGES * HEAD_TILE_BYTES);
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_bias + nbias);
+    uint64_t *full = s_bar, *empty = s_bar + HEAD_STAGES, *act_ready = empty + HEAD_STAGES,
+             *layer_done = act_ready + 1, *fin_done = layer_done + 1, *fin_free = fin_done + 2;
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(fin_free + 2);
+
+    if (tid == 0) {
+        for (int i = 0; i < HEAD_STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
+        ptx::mbar_init(act_ready, 128);
+        ptx::mbar_init(layer_done, 1);
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&fin_done[i], 1); ptx::mbar_init(&fin_free[i], 128); }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 5) ptx::tmem_alloc(s_tmem, 512);
+    for (int e = tid; e < nbias; e += HEAD_THREADS) s_bias[e] = __ldg(a.bias + e);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+    constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
+
+    if (warp == 4) {
+        // ===================== weight producer: stream every tile of every layer, once per row tile ============
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+                const uint8_t *src = reinterpret_cast<const uint8_t *>(a.w);
+                for (int l = 0; l < HEAD_LAYERS; ++l)
+                    for (int nc = 0; nc < a.out[l] / 128; ++nc)
+                        for (int k0 = 0; k0 < a.Kp[l]; k0 += HEAD_KT, ++it) {
+                            const uint32_t bytes = 128u * min(HEAD_KT, a.Kp[l] - k0) * 2;
+                            const int st = it % HEAD_STAGES;
+                            ptx::mbar_wait(&empty[st], ((it / HEAD_STAGES) & 1) ^ 1);
+                            ptx::mbar_expect_tx(&full[st], bytes);
+                            ptx::bulk_g2s(s_wt + st * HEAD_TILE_BYTES, src, bytes, &full[st]);
+                            src += bytes;
+                        }
+            }
+        }
+    } else if (warp == 5) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t act = ptx::smem_u32(s_act), wt = ptx::smem_u32(s_wt);
+            uint32_t it = 0, n_ready = 0, fin_use[2] = {0, 0};
+            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+                for (int l = 0; l < HEAD_LAYERS; ++l) {
+                    ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
+                    ptx::tc_fence_after();
+                    const bool last = l == HEAD_LAYERS - 1;
+                    for (int nc = 0; nc < a.out[l] / 128; ++nc) {
+                        uint32_t dcol = tmem_base + nc * 128;
+                        if (last) {
+                            const int buf = nc & 1;
+                            if (fin_use[buf] > 0) {
+                                ptx::mbar_wait(&fin_free[buf], (fin_use[buf] - 1) & 1);
+                                ptx::tc_fence_after();
+                            }
+                            ++fin_use[buf];
+                            dcol = tmem_base + buf * 128;
+                        }
+                        for (int k0 = 0; k0 < a.Kp[l]; k0 += HEAD_KT, ++it) {
+                            const int st = it % HEAD_STAGES;
+                            ptx::mbar_wait(&full[st], (it / HEAD_STAGES) & 1);
+                            ptx::tc_fence_after();
+                            const int kt = min(HEAD_KT, a.Kp[l] - k0);
+                            const uint32_t wtile = wt + st * HEAD_TILE_BYTES;
+                            for (int ks = 0; ks < kt / 16; ++ks) {
+                                const uint64_t xd = make_sdesc(act + ((k0 >> 3) + ks * 2) * TC_LBO, TC_LBO);
+                                const uint64_t wd = make_sdesc(wtile + ks * 2 * TC_LBO, TC_LBO);
+                                if (!last) ptx::mma_f16_ss(dcol, xd, wd, IDESC, (k0 | ks) > 0);
+                                else ptx::mma_f16_ss(dcol, wd, xd, IDESC, (k0 | ks) > 0);   // transposed
+                            }
+                            ptx::mma_commit(&empty[st]);               // frees the weight stage when the MMAs retire
+                        }
+                        if (last) ptx::mma_commit(&fin_done[nc & 1]);
+                    }
+                    if (!last) ptx::mma_commit(layer_done);
+                }
+            }
+        }
+    } else {
+        // ===================== row build + epilogues =====================
+        const int r = warp * 32 + lane;
+        const uint32_t act_row = ptx::smem_u32(s_act) + r * 16;
+        const uint32_t tlane = tmem_base + ((uint32_t)(warp * 32) << 16);
+        uint32_t n_done = 0, fin_cnt[2] = {0, 0};
+        const int C0 = a.C0, n = a.n;
+        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            const int b = tile / a.tiles_per_pair;
+            const int p0 = (tile - b * a.tiles_per_pair) * 128;
+            const int pt = p0 + r;
+            // ---- input rows: [motion feat (C0) | xyz (3) | 0]
+            if (pt < n) {
+                const size_t row = (size_t)b * n + pt;
+                const float4 *f = reinterpret_cast<const float4 *>(a.feat + row * C0);
+#pragma unroll 4
+                for (int c = 0; c < C0 / 8; ++c) {
+                    const float4 u0 = __ldg(f + 2 * c), u1 = __ldg(f + 2 * c + 1);
+                    st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
+                                 Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
+                }
+                const float *p3 = a.xyz + row * 3;
+                store_coord_chunks<T16>(act_row + (C0 / 8) * TC_LBO, act_row + (C0 / 8 + 1) * TC_LBO, __ldg(p3),
+                                        __ldg(p3 + 1), __ldg(p3 + 2));
+                for (int c = C0 / 8 + 2; c < a.Kp[0] / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+            } else {
+                for (int c = 0; c < a.Kp[0] / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+            }
+            ptx::fence_proxy_async_smem();
+            ptx::mbar_arrive(act_ready);
+            // ---- hidden layers: accumulators -> activations, in place
+            int boff = 0;
+            for (int l = 0; l < HEAD_LAYERS - 1; ++l) {
+                ptx::mbar_wait(layer_done, n_done & 1); ++n_done;
+                ptx::tc_fence_after();
+                epilogue_hidden<T16>(tlane, a.out[l], s_bias + boff, act_row);
+                boff += a.out[l];
+                ptx::tc_fence_before();
+                ptx::fence_proxy_async_smem();
+                ptx::mbar_arrive(act_ready);
+            }
+            // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points
+            const int nvalid = min(128, n - p0);
+            for (int nc = 0; nc < a.out[HEAD_LAYERS - 1] / 128; ++nc) {
+                const int buf = nc & 1;
+                ptx::mbar_wait(&fin_done[buf], fin_cnt[buf] & 1); ++fin_cnt[buf];
+                ptx::tc_fence_after();
+                float cur = -INFINITY;
+#pragma unroll
+                for (int c0 = 0; c0 < 128; c0 += 32) {
+                    uint32_t v[32];
+                    ptx::tmem_ld32(tlane + buf * 128 + c0, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c0 + i < nvalid) cur = fmaxf(cur, __uint_as_float(v[i]));
+                }
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&fin_free[buf]);
+                const int ch = nc * 128 + r;
+                const float val = fmaxf(cur + s_bias[boff + ch], 0.f);
+                // post-ReLU values are >= 0: their int image is order preserving
+                atomicMax(reinterpret_cast<int *>(a.pooled) + (size_t)b * a.out[HEAD_LAYERS - 1] + ch,
+                          __float_as_int(val));
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 5) ptx::tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------- host side
+struct TcModel {
+    int fmt;                      // 1 bf16, 2 fp16
+    int F, k, K0p, H3;
+    float radius;
+    uint16_t *flow_w = nullptr;   // packed flow weights
+    float *flow_b = nullptr;
+    uint16_t *head_w = nullptr;   // packed head weight tiles
+    float *head_b = nullptr;
+    int head_Kp[HEAD_LAYERS], head_out[HEAD_LAYERS], head_act_k;
+    size_t flow_smem, head_smem;
+    int num_sms;
+};
+
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+template <typename T16>
+static int pack_rows(const float *W, int out, int in, int nfeat, int row0, int R, int k0, int Kt, uint16_t *dst) {
+    pack_tile_kernel<T16><<<div_up(R * Kt, 256), 256>>>(W, out, in, nfeat, row0, R, k0, Kt, dst);
+    DCLR_LAUNCH_CHECK("pack_tile_kernel");
+    return DCLR_OK;
+}
+
+static int pack_any(int fmt, const float *W, int out, int in, int nfeat, int row0, int R, int k0, int Kt,
+                    uint16_t *dst) {
+    return fmt == 1 ? pack_rows<__nv_bfloat16>(W, out, in, nfeat, row0, R, k0, Kt, dst)
+                    : pack_rows<__half>(W, out, in, nfeat, row0, R, k0, Kt, dst);
+}
+
+void tc_destroy(TcModel *t) {
+    if (!t) return;
+    if (t->flow_w) cudaFree(t->flow_w);
+    if (t->flow_b) cudaFree(t->flow_b);
+    if (t->head_w) cudaFree(t->head_w);
+    if (t->head_b) cudaFree(t->head_b);
+    delete t;
+}
+
+int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcModel **out) {
+    // shapes this path is built for (the reference model configs); anything else must use numerics fp32
+    if (F % 8 || F < 8) return fail(DCLR_E_UNSUPPORTED, "tensor-core path: feature width %d is not a multiple of 8", F);
+    if (sp[0].in != 2 * F + 3 || sp[0].out != 128 || sp[1].in != 128 || sp[1].out != 128 || sp[2].in != 128 ||
+        sp[2].out % 128 || sp[2].out > 256)
+        return fail(DCLR_E_UNSUPPORTED, "tensor-core path: merge MLP must be [%d,128,128,128|256]", 2 * F + 3);
+    if (k < 1 || k > 128) return fail(DCLR_E_UNSUPPORTED, "tensor-core path: k must be in [1,128]");
+    const int H3 = sp[2].out;
+    if (sp[3].in != H3 + 3) return fail(DCLR_E_UNSUPPORTED, "tensor-core path: head input width mismatch");
+    for (int l = 0; l < HEAD_LAYERS; ++l) {
+        const TcLayerSpec &s = sp[3 + l];
+        if (s.out % 128 || (l < HEAD_LAYERS - 1 && s.out > 512) || (l > 0 && (s.in != sp[2 + l].out || s.in % 16)))
+            return fail(DCLR_E_UNSUPPORTED, "tensor-core path: head layer %d shape [%d -> %d] not supported", l, s.in,
+                        s.out);
+    }
+    TcModel *t = new (std::nothrow) TcModel();
+    if (!t) return fail(DCLR_E_INVALID, "out of host memory");
+    t->fmt = fmt; t->F = F; t->k = k; t->radius = radius; t->H3 = H3;
+    t->K0p = round_up(2 * F + 9, 16);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&t->num_sms, cudaDevAttrMultiProcessorCount, dev);
+    int rc = DCLR_OK;
+    auto bail = [&](int code) { tc_destroy(t); return code; };
+#define TC_CUDA(expr)                                                                        \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess)                                                              \
+            return bail(fail(DCLR_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__))); \
+    } while (0)
+
+    // ---- flow: W1 [128 x K0p] | W2 [128 x 128] | W3 in 128-row blocks [H3 x 128]; biases b1 b2 b3
+    const size_t flow_elems = (size_t)128 * t->K0p + 128 * 128 + (size_t)H3 * 128;
+    TC_CUDA(cudaMalloc(&t->flow_w, flow_elems * 2));
+    TC_CUDA(cudaMalloc(&t->flow_b, (256 + H3) * sizeof(float)));
+    uint16_t *p = t->flow_w;
+    if ((rc = pack_any(fmt, sp[0].W, 128, sp[0].in, 2 * F, 0, 128, 0, t->K0p, p))) return bail(rc);
+    p += (size_t)128 * t->K0p;
+    if ((rc = pack_any(fmt, sp[1].W, 128, 128, 0, 0, 128, 0, 128, p))) return bail(rc);
+    p += 128 * 128;
+    for (int mb = 0; mb < H3 / 128; ++mb, p += 128 * 128)
+        if ((rc = pack_any(fmt, sp[2].W, H3, 128, 0, mb * 128, 128, 0, 128, p))) return bail(rc);
+    TC_CUDA(cudaMemcpy(t->flow_b, sp[0].b, 128 * 4, cudaMemcpyDeviceToDevice));
+    TC_CUDA(cudaMemcpy(t->flow_b + 128, sp[1].b, 128 * 4, cudaMemcpyDeviceToDevice));
+    TC_CUDA(cudaMemcpy(t->flow_b + 256, sp[2].b, H3 * 4, cudaMemcpyDeviceToDevice));
+    t->flow_smem = (size_t)128 * t->K0p * 2 + 128 * 128 * 2 + (size_t)H3 * 128 * 2 +
+                   (size_t)FLOW_SLOTS * 128 * t->K0p * 2 + (256 + H3) * 4 + FLOW_SLOTS * 4 * 4 +
+                   (1 + 2 * FLOW_SLOTS) * 8 + 16;
+
+    // ---- head: tiles in (layer, 128-row block, 64-wide K block) order
+    size_t head_elems = 0;
+    int nbias = 0;
+    t->head_act_k = 0;
+    for (int l = 0; l < HEAD_LAYERS; ++l) {
+        t->head_Kp[l] = round_up(l == 0 ? H3 + 9 : sp[3 + l].in, 16);
+        t->head_out[l] = sp[3 + l].out;
+        head_elems += (size_t)t->head_out[l] * t->head_Kp[l];
+        nbias += t->head_out[l];
+        if (t->head_Kp[l] > t->head_act_k) t->head_act_k = t->head_Kp[l];
+        if (l < HEAD_LAYERS - 1 && t->head_out[l] > t->head_act_k) t->head_act_k = t->head_out[l];
+    }
+    TC_CUDA(cudaMalloc(&t->head_w, head_elems * 2));
+    TC_CUDA(cudaMalloc(&t->head_b, nbias * sizeof(float)));
+    p = t->head_w;
+    int boff = 0;
+    for (int l = 0; l < HEAD_LAYERS; ++l) {
+        const TcLayerSpec &s = sp[3 + l];
+        for (int nc = 0; nc < s.out / 128; ++nc)
+            for (int k0 = 0; k0 < t->head_Kp[l]; k0 += HEAD_KT) {
+                const int kt = t->head_Kp[l] - k0 < HEAD_KT ? t->head_Kp[l] - k0 : HEAD_KT;
+                if ((rc = pack_any(fmt, s.W, s.out, s.in, l == 0 ? H3 : 0, nc * 128, 128, k0, kt, p))) return bail(rc);
+                p += (size_t)128 * kt;
+            }
+        TC_CUDA(cudaMemcpy(t->head_b + boff, s.b, s.out * 4, cudaMemcpyDeviceToDevice));
+        boff += s.out;
+    }
+    t->head_smem = (size_t)128 * t->head_act_k * 2 + HEAD_STAGES * HEAD_TILE_BYTES + (size_t)nbias * 4 +
+                   (2 * HEAD_STAGES + 6) * 8 + 16;
+    TC_CUDA(cudaDeviceSynchronize());
+    if (t->flow_smem > 232448 || t->head_smem > 232448)
+        return bail(fail(DCLR_E_UNSUPPORTED, "tensor-core path: shared memory budget exceeded (%zu / %zu bytes)",
+                         t->flow_smem, t->head_smem));
+    if (fmt == 1) {
+        TC_CUDA(cudaFuncSetAttribute(flow_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)t->flow_smem));
+        TC_CUDA(cudaFuncSetAttribute(head_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)t->head_smem));
+    } else {
+        TC_CUDA(cudaFuncSetAttribute(flow_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)t->flow_smem));
+        TC_CUDA(cudaFuncSetAttribute(head_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)t->head_smem));
+    }
+#undef TC_CUDA
+    *out = t;
+    return DCLR_OK;
+}
+
+int tc_flow(TcModel *t, const float *xyz, const float *feat, const int32_t *nbr, int B, int n, float *motion,
+            cudaStream_t st) {
+    FlowArgs fa;
+    fa.xyz = xyz; fa.feat = feat; fa.nbr = nbr; fa.w = t->flow_w; fa.bias = t->flow_b; fa.out = motion;
+    fa.B = B; fa.n = n; fa.k = t->k; fa.F = t->F; fa.K0p = t->K0p; fa.H3 = t->H3; fa.radius = t->radius;
+    fa.groups_per_tile = 128 / t->k;
+    fa.tiles_per_pair = div_up(n, fa.groups_per_tile);
+    fa.num_tiles = B * fa.tiles_per_pair;
+    const int grid = std::min(t->num_sms, div_up(fa.num_tiles, FLOW_SLOTS));
+    if (t->fmt == 1) flow_tc_kernel<__nv_bfloat16><<<grid, FLOW_THREADS, t->flow_smem, st>>>(fa);
+    else flow_tc_kernel<__half><<<grid, FLOW_THREADS, t->flow_smem, st>>>(fa);
+    DCLR_LAUNCH_CHECK("flow_tc_kernel");
+    return DCLR_OK;
+}
+
+int tc_head(TcModel *t, const float *xyz, const float *motion, int B, int n, float *pooled, cudaStream_t st) {
+    HeadArgs ha;
+    ha.feat = motion; ha.xyz = xyz; ha.w = t->head_w; ha.bias = t->head_b; ha.pooled = pooled;
+    ha.B = B; ha.n = n; ha.C0 = t->H3;
+    for (int l = 0; l < HEAD_LAYERS; ++l) { ha.Kp[l] = t->head_Kp[l]; ha.out[l] = t->head_out[l]; }
+    ha.tiles_per_pair = div_up(n, 128);
+    ha.num_tiles = B * ha.tiles_per_pair;
+    ha.act_k = t->head_act_k;
+    const int grid = std::min(t->num_sms, ha.num_tiles);
+    DCLR_CUDA(cudaMemsetAsync(pooled, 0, (size_t)B * t->head_out[HEAD_LAYERS - 1] * sizeof(float), st));
+    if (t->fmt == 1) head_tc_kernel<__nv_bfloat16><<<grid, HEAD_THREADS, t->head_smem, st>>>(ha);
+    else head_tc_kernel<__half><<<grid, HEAD_THREADS, t->head_smem, st>>>(ha);
+    DCLR_LAUNCH_CHECK("head_tc_kernel");
+    return DCLR_OK;
+}
+
+int tc_format(const TcModel *t) { return t->fmt; }
+
 }  // namespace dclr

@@ -91,9 +91,9 @@ static int ensure_ws(dclr_model *m, int G, int N, int B) {
 }
 
 // stages a forward is split into for timing
-enum { ST_FPS = 0, ST_BALL, ST_SA, ST_KNN, ST_DENSE, ST_TAIL, ST_LAYOUT, ST_COUNT };
+enum { ST_FPS = 0, ST_BALL, ST_SA, ST_KNN, ST_FLOW, ST_HEAD, ST_TAIL, ST_LAYOUT, ST_COUNT };
 static const char *const kStageNames[ST_COUNT] = {"fps", "ball_query", "sa_mlp_maxpool", "knn",
-                                                  "flow_embed_head", "pose_tail", "layout"};
+                                                  "flow_embed", "pose_head_conv", "pose_tail", "layout"};
 constexpr int EV_RING = 64;
 constexpr int EV_PER_CALL = 2 * ST_COUNT;      // begin/end per stage
 
@@ -158,12 +158,15 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
         StageScope sc(m, ST_KNN, st);
         DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, st));
     }
-    timing_mark(m, ST_DENSE, 0, st);
-    if (m->numerics == 1) {
-        int rc = tc_merge_output(m->tc, m->new_xyz, m->sa_feat, m->knn_col, B, M, m->motion, ldm, m->pooled, st,
-                                 &m->last_launches);
-        if (rc != DCLR_OK) return rc;
+    if (m->numerics != 0) {
+        {
+            StageScope sc(m, ST_FLOW, st);
+            DCLR_TRY(tc_flow(m->tc, m->new_xyz, m->sa_feat, m->knn_col, B, M, m->motion, st));
+        }
+        StageScope sc(m, ST_HEAD, st);
+        DCLR_TRY(tc_head(m->tc, m->new_xyz, m->motion, B, M, m->pooled, st));
     } else {
+        timing_mark(m, ST_FLOW, 0, st);
         const int ld0 = (int)align_up(m->nmerge_in, 4);
         DCLR_TRY(flow_rows_launch(m->new_xyz, m->sa_feat, m->knn_col, B, M, k, F, a.merge_radius, m->rows, ld0,
                                   m->mask, st));
@@ -175,6 +178,8 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
                                    a.merge_mlp[2], a.merge_mlp[1], 1, st));
         DCLR_TRY(masked_groupmax_launch(m->h3, a.merge_mlp[2], m->mask, m->new_xyz, BM, k, a.merge_mlp[2], m->motion,
                                         ldm, st));
+        timing_mark(m, ST_FLOW, 1, st);
+        timing_mark(m, ST_HEAD, 0, st);
         const float *in = m->motion;
         int ldin = ldm, kin = m->head_in;
         float *bufs[2] = {m->actA, m->actB};
@@ -185,8 +190,8 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
             in = out; ldin = a.out_mlp[l]; kin = a.out_mlp[l];
         }
         DCLR_TRY(rowmax_launch(in, ldin, B, M, a.out_mlp[4], m->pooled, st));
+        timing_mark(m, ST_HEAD, 1, st);
     }
-    timing_mark(m, ST_DENSE, 1, st);
     timing_mark(m, ST_TAIL, 0, st);
     // fully connected tail: helper.py:97-123 (ReLU after both), final nn.Linear, activation deepclr.py:275-282
     DCLR_TRY(linear_f32_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
@@ -199,7 +204,10 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     timing_mark(m, ST_TAIL, 1, st);
     if (motion_out) {
         StageScope sc(m, ST_LAYOUT, st);
-        DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, ldm, 0, B, M, a.merge_mlp[2], motion_out, st));
+        if (m->numerics != 0)    // tensor-core path keeps features only; coordinates are the template samples
+            DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->motion, a.merge_mlp[2], 0, B, M, a.merge_mlp[2], motion_out, st));
+        else
+            DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, ldm, 0, B, M, a.merge_mlp[2], motion_out, st));
     }
     return DCLR_OK;
 }
@@ -282,12 +290,16 @@ extern "C" void dclr_model_destroy(dclr_model *m) {
 
 extern "C" int dclr_model_set_numerics(dclr_model *m, int mode) {
     DCLR_CHECK_ARG(m, "null model");
-    DCLR_CHECK_ARG(mode == 0 || mode == 1, "numerics mode must be 0 (fp32) or 1 (bf16 tensor cores)");
-    if (mode == 1 && !m->tc) {
+    DCLR_CHECK_ARG(mode >= 0 && mode <= 2, "numerics mode must be 0 (fp32), 1 (bf16) or 2 (fp16 tensor cores)");
+    if (mode != 0 && m->tc && tc_format(m->tc) != mode) {
+        tc_destroy(m->tc);
+        m->tc = nullptr;
+    }
+    if (mode != 0 && !m->tc) {
         TcLayerSpec specs[8];
         for (int l = 0; l < 3; ++l) specs[l] = {m->merge[l].W, m->merge[l].b, m->merge[l].out, m->merge[l].in};
         for (int l = 0; l < 5; ++l) specs[3 + l] = {m->outc[l].W, m->outc[l].b, m->outc[l].out, m->outc[l].in};
-        int rc = tc_create(specs, m->F, m->arch.knn_k, m->arch.merge_radius, &m->tc);
+        int rc = tc_create(specs, m->F, m->arch.knn_k, m->arch.merge_radius, mode, &m->tc);
         if (rc != DCLR_OK) return rc;
     }
     m->numerics = mode;

@@ -330,7 +330,7 @@ class DeepCLR(BaseModel):
         else:
             self._loss_layer = init_loss_module(_as_cfg(loss), label_type, **kwargs)
         # fused route state
-        self.numerics = os.environ.get('DCLR_NUMERICS', 'fp32')   # 'fp32' | 'bf16'
+        self.numerics = os.environ.get('DCLR_NUMERICS', 'fp32')   # 'fp32' | 'fp16' | 'bf16' (include/deepclr_b200.h)
         self._native: Optional[NativeModel] = None
         self._native_key = None
 

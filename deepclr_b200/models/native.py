@@ -42,7 +42,7 @@ class NativeModel:
         with torch.cuda.device(device):
             _lib.check(_lib.lib().dclr_model_create(ctypes.byref(arch), ctypes.c_void_p(flat.data_ptr()),
                                                     flat.numel(), ctypes.byref(self._handle)), 'dclr_model_create')
-            _lib.check(_lib.lib().dclr_model_set_numerics(self._handle, {'fp32': 0, 'bf16': 1}[numerics]),
+            _lib.check(_lib.lib().dclr_model_set_numerics(self._handle, {'fp32': 0, 'bf16': 1, 'fp16': 2}[numerics]),
                        'dclr_model_set_numerics')
         self.numerics = numerics
         self.label_dim = {0: 6, 1: 7, 2: 8}[arch.label_type]

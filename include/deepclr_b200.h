@@ -97,7 +97,8 @@ typedef struct {
  */
 int dclr_model_create(const dclr_arch *arch, const float *weights, size_t num_floats, dclr_model **out);
 void dclr_model_destroy(dclr_model *m);
-/* numerics: 0 = fp32 SIMT everywhere (fp32-faithful), 1 = bf16 tcgen05 tensor-core MLPs (fp32 accumulate) */
+/* numerics: 0 = fp32 SIMT everywhere (fp32-faithful); 1 = bf16, 2 = fp16 operands on the tcgen05 tensor cores
+ * (fp32 accumulation in TMEM) for the flow-embedding and pose-head MLP stacks */
 int dclr_model_set_numerics(dclr_model *m, int mode);
 
 /*
