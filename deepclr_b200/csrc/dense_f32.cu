@@ -70,6 +70,72 @@ int linear_f32_launch(const float *X, int ldx, const float *W, const float *b, f
     return DCLR_OK;
 }
 
+// ---------------------------------------------------------------- skinny linear for the pose tail (few rows)
+// Y[M,N] = act(X[M,K] W[N,K]^T + b) when M is a batch of pooled vectors: one warp per output column n, 32 rows per
+// block in registers; the weight row streams through once per row block, X rows are re-read from L1/L2 (coalesced
+// float4).  act: 0 none, 1 ReLU, 2 pose activation of `label_type` (deepclr.py:275-282).  Needs K % 4 == 0.
+constexpr int SK_ROWS = 32, SK_WARPS = 8;
+
+__device__ __forceinline__ float pose_act(float v, int c, int label_type) {
+    if (label_type == 2) {
+        if (c == 0) v = 1.f / (1.f + expf(-v));
+        else if (c < 4) v = tanhf(v);
+    } else if (label_type == 1) {
+        if (c == 3) v = 1.f / (1.f + expf(-v));
+        else if (c > 3) v = tanhf(v);
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(SK_WARPS * 32)
+linear_skinny_kernel(const float *__restrict__ X, int ldx, const float *__restrict__ W, const float *__restrict__ bias,
+                     float *__restrict__ Y, int ldy, int M, int N, int K, int act, int label_type) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = blockIdx.x * SK_WARPS + warp;
+    const int m0 = blockIdx.y * SK_ROWS;
+    if (n >= N) return;
+    float acc[SK_ROWS];
+#pragma unroll
+    for (int i = 0; i < SK_ROWS; ++i) acc[i] = 0.f;
+    const float *wrow = W + (size_t)n * K;
+    for (int k0 = lane * 4; k0 < K; k0 += 128) {
+        const float4 w = __ldg(reinterpret_cast<const float4 *>(wrow + k0));
+#pragma unroll
+        for (int i = 0; i < SK_ROWS; ++i) {
+            const int m = m0 + i < M ? m0 + i : M - 1;
+            const float4 xv = __ldg(reinterpret_cast<const float4 *>(X + (size_t)m * ldx + k0));
+            acc[i] = fmaf(w.x, xv.x, acc[i]);
+            acc[i] = fmaf(w.y, xv.y, acc[i]);
+            acc[i] = fmaf(w.z, xv.z, acc[i]);
+            acc[i] = fmaf(w.w, xv.w, acc[i]);
+        }
+    }
+    float mine = 0.f;
+#pragma unroll
+    for (int i = 0; i < SK_ROWS; ++i) {
+        float v = acc[i];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        if (lane == i) mine = v;
+    }
+    const int m = m0 + lane;
+    if (m < M) {
+        float v = mine + __ldg(bias + n);
+        if (act == 1) v = fmaxf(v, 0.f);
+        else if (act == 2) v = pose_act(v, n, label_type);
+        Y[(size_t)m * ldy + n] = v;
+    }
+}
+
+int linear_skinny_launch(const float *X, int ldx, const float *W, const float *b, float *Y, int ldy, int M, int N,
+                         int K, int act, int label_type, cudaStream_t st) {
+    if (K % 4 || ldx % 4) return fail(DCLR_E_UNSUPPORTED, "linear_skinny: K and ldx must be multiples of 4");
+    dim3 grid(div_up(N, SK_WARPS), div_up(M, SK_ROWS));
+    linear_skinny_kernel<<<grid, SK_WARPS * 32, 0, st>>>(X, ldx, W, b, Y, ldy, M, N, K, act, label_type);
+    DCLR_LAUNCH_CHECK("linear_skinny_kernel");
+    return DCLR_OK;
+}
+
 // ---------------------------------------------------------------- flow embedding rows
 // row (b,i,j): [ p_src(nbr) - p_tmpl(i) | f_tmpl(i) | f_src(nbr) ]  (deepclr.py:206-210), plus the radius mask
 // (deepclr.py:220-222).  xyz [2B,n,3], feat [2B,n,F] point-major, templates first.

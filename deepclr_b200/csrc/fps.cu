@@ -1,5 +1,6 @@
 // Farthest point sampling for sm_100a: one CTA per cloud, the cloud held in shared memory (SoA) and, per thread,
-// in registers; min-distance state never leaves registers; argmax = two redux.sync steps + one shared atomicMin.
+// in registers (as packed fp32x2 pairs); min-distance state never leaves registers; argmax = redux.sync within
+// the warp, one shared-memory slot per warp, ONE __syncthreads per round.
 //
 // Replaces furthest_point_sampling_kernel + gather_points_kernel_fast of the reference
 // (extern/Pointnet2.PyTorch/pointnet2/src/sampling_gpu.cu:94-209, :8-24).  Arithmetic per round and point k is the
@@ -15,20 +16,54 @@ namespace dclr {
 
 constexpr int FPS_MAX_RESIDENT_N = 16384;
 
-// T threads, PPT points per thread (strided ownership k = tid + i*T), ZS: read z from shared memory instead of
-// registers (needed at T=1024, PPT=16 where only 64 registers per thread exist).
-template <int T, int PPT, bool ZS>
+// Packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2): two points per instruction, each half rounded exactly like
+// the scalar IEEE op, so the result is bit-identical to the scalar expression above.
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+
+// T threads, PP point PAIRS per thread: thread tid owns points 2*(tid + i*T) and 2*(tid + i*T) + 1, i < PP.
+// ZS: read z from shared memory (one 8-byte load per pair) instead of registers -- needed at T=1024, PP=8 where only
+// 64 registers per thread exist.  One __syncthreads per round: every warp publishes (max, lowest index at max) into
+// a parity-double-buffered slot, then every warp reduces the <= 32 slots redundantly.
+template <int T, int PP, bool ZS>
 __global__ void __launch_bounds__(T, 1)
 fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int32_t *__restrict__ idx_out,
                     float *__restrict__ new_xyz_out) {
     extern __shared__ __align__(16) float smem[];
-    float *s_x = smem, *s_y = smem + N, *s_z = smem + 2 * N;
-    int *s_wmax = reinterpret_cast<int *>(smem + 3 * N);   // [32]
-    int *s_win = s_wmax + 32;                              // [2]
+    const int NP = (N + 1) & ~1;                                   // even padded length
+    float *s_x = smem, *s_y = smem + NP, *s_z = smem + 2 * NP;
+    int2 *s_res = reinterpret_cast<int2 *>(smem + 3 * NP);          // [2][32]
 
     const int b = blockIdx.x;
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = T / 32;
     pts += (size_t)b * N * stride;
     idx_out += (size_t)b * npoint;
     if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
@@ -46,18 +81,20 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
             s_x[k] = __ldg(p); s_y[k] = __ldg(p + 1); s_z[k] = __ldg(p + 2);
         }
     }
-    if (tid < 2) s_win[tid] = INT_MAX;
+    if (tid == 0 && NP > N) { s_x[N] = 0.f; s_y[N] = 0.f; s_z[N] = 0.f; }
     __syncthreads();
 
-    float x[PPT], y[PPT], z[ZS ? 1 : PPT], t[PPT];
+    uint64_t x2[PP], y2[PP], z2[ZS ? 1 : PP];
+    float tl[PP], th[PP];
 #pragma unroll
-    for (int i = 0; i < PPT; ++i) {
-        int k = tid + i * T;
-        bool ok = k < N;
-        x[i] = ok ? s_x[k] : 0.f;
-        y[i] = ok ? s_y[k] : 0.f;
-        if (!ZS) z[i] = ok ? s_z[k] : 0.f;
-        t[i] = ok ? 1e10f : -1.0f;     // -1 can never win (reference: best starts at -1, strict >)
+    for (int i = 0; i < PP; ++i) {
+        const int k = 2 * (tid + i * T);
+        const bool ok = k < NP;                                   // NP even: the pair is inside the padded arrays
+        x2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_x + k) : 0ull;
+        y2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_y + k) : 0ull;
+        if (!ZS) z2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_z + k) : 0ull;
+        tl[i] = k < N ? 1e10f : -1.0f;        // -1 can never win (reference: best starts at -1, strict >)
+        th[i] = k + 1 < N ? 1e10f : -1.0f;
     }
 
     int old = 0;
@@ -67,31 +104,44 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
         if (tid == 0 && new_xyz_out) {
             new_xyz_out[(j - 1) * 3 + 0] = x1; new_xyz_out[(j - 1) * 3 + 1] = y1; new_xyz_out[(j - 1) * 3 + 2] = z1;
         }
+        const uint64_t xo = pack2(x1, x1), yo = pack2(y1, y1), zo = pack2(z1, z1);
         float best = -1.0f;
 #pragma unroll
-        for (int i = 0; i < PPT; ++i) {
-            float zz;
-            if (ZS) { int k = tid + i * T; zz = s_z[k < N ? k : 0]; } else zz = z[i];
-            float d = sqdist_pn2(x[i] - x1, y[i] - y1, zz - z1);
-            t[i] = fminf(d, t[i]);
-            best = fmaxf(best, t[i]);
+        for (int i = 0; i < PP; ++i) {
+            uint64_t zz;
+            if (ZS) {
+                const int k = 2 * (tid + i * T);
+                zz = *reinterpret_cast<const uint64_t *>(s_z + (k < NP ? k : 0));
+            } else {
+                zz = z2[i];
+            }
+            const uint64_t dx = sub2(x2[i], xo), dy = sub2(y2[i], yo), dz = sub2(zz, zo);
+            const uint64_t d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+            float dl, dh;
+            unpack2(d2, dl, dh);
+            tl[i] = fminf(dl, tl[i]);
+            th[i] = fminf(dh, th[i]);
+            best = max3(best, tl[i], th[i]);
         }
-        // block max of the (non-negative) float through its integer image
-        int wb = __reduce_max_sync(0xffffffffu, __float_as_int(best));
-        if (lane == 0) s_wmax[warp] = wb;
-        __syncthreads();
-        int v = lane < (T / 32) ? s_wmax[lane] : INT_MIN;
-        const int m = __reduce_max_sync(0xffffffffu, v);
-        if (tid == 0) s_win[(j + 1) & 1] = INT_MAX;          // re-arm the other slot for the next round
-        if (__float_as_int(best) == m) {
-            int cand = INT_MAX;
+        // warp: max value (through its integer image; -1.0f is a negative int) and the lowest index holding it
+        const int bi = __float_as_int(best);
+        const int wm = __reduce_max_sync(0xffffffffu, bi);
+        int cand = INT_MAX;
+        if (bi == wm) {
 #pragma unroll
-            for (int i = PPT - 1; i >= 0; --i)
-                if (__float_as_int(t[i]) == m) cand = tid + i * T;   // lowest i (= lowest index) survives
-            atomicMin(&s_win[j & 1], cand);
+            for (int i = PP - 1; i >= 0; --i) {                  // descending: the lowest index survives
+                const int k = 2 * (tid + i * T);
+                cand = __float_as_int(th[i]) == wm ? k + 1 : cand;
+                cand = __float_as_int(tl[i]) == wm ? k : cand;
+            }
         }
+        const int wi = __reduce_min_sync(0xffffffffu, cand);
+        int2 *slot = s_res + (j & 1) * 32;
+        if (lane == 0) slot[warp] = make_int2(wm, wi);
         __syncthreads();
-        old = s_win[j & 1];
+        const int2 e = lane < NW ? slot[lane] : make_int2(INT_MIN, INT_MAX);
+        const int m = __reduce_max_sync(0xffffffffu, e.x);
+        old = __reduce_min_sync(0xffffffffu, e.x == m ? e.y : INT_MAX);
         if (tid == 0) idx_out[j] = old;
     }
     if (tid == 0 && new_xyz_out && npoint > 0) {
@@ -148,11 +198,11 @@ fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, 
     }
 }
 
-template <int T, int PPT, bool ZS>
+template <int T, int PP, bool ZS>
 static int launch_resident(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx,
                            cudaStream_t st) {
-    size_t smem = (size_t)3 * N * sizeof(float) + 34 * sizeof(int);
-    auto kern = fps_resident_kernel<T, PPT, ZS>;
+    size_t smem = (size_t)3 * ((N + 1) & ~1) * sizeof(float) + 64 * sizeof(int2);
+    auto kern = fps_resident_kernel<T, PP, ZS>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<B, T, smem, st>>>(pts, stride, N, npoint, idx, nx);
     DCLR_LAUNCH_CHECK("fps_resident_kernel");
@@ -161,14 +211,14 @@ static int launch_resident(const float *pts, int stride, int B, int N, int npoin
 
 int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, float *temp_big,
                cudaStream_t st) {
-    if (N <= 128) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 256) return launch_resident<128, 2, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 512) return launch_resident<128, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 1024) return launch_resident<128, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 2048) return launch_resident<256, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 4096) return launch_resident<256, 16, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 8192) return launch_resident<512, 16, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= FPS_MAX_RESIDENT_N) return launch_resident<1024, 16, true>(pts, stride, B, N, npoint, idx, nx, st);
+    // T threads x PP pairs x 2 points >= N
+    if (N <= 256) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 512) return launch_resident<128, 2, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 1024) return launch_resident<128, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 2048) return launch_resident<256, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 4096) return launch_resident<256, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 8192) return launch_resident<512, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= FPS_MAX_RESIDENT_N) return launch_resident<1024, 8, true>(pts, stride, B, N, npoint, idx, nx, st);
     if (!temp_big) return fail(DCLR_E_INVALID, "fps: N=%d needs a scratch buffer", N);
     fps_stream_kernel<1024><<<B, 1024, 0, st>>>(pts, stride, N, npoint, temp_big, idx, nx);
     DCLR_LAUNCH_CHECK("fps_stream_kernel");

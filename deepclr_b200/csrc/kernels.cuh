@@ -33,6 +33,8 @@ int sa_mlp_launch(const SaArgs &a, int B, int cin, const int *h, cudaStream_t st
 // dense_f32.cu
 int linear_f32_launch(const float *X, int ldx, const float *W, const float *b, float *Y, int ldy, int M, int N, int K,
                       int relu, cudaStream_t st);
+int linear_skinny_launch(const float *X, int ldx, const float *W, const float *b, float *Y, int ldy, int M, int N,
+                         int K, int act, int label_type, cudaStream_t st);
 int flow_rows_launch(const float *xyz, const float *feat, const int32_t *nbr, int B, int n, int k, int F, float radius,
                      float *rows, int ld, uint8_t *mask, cudaStream_t st);
 int masked_groupmax_launch(const float *H, int ldh, const uint8_t *mask, const float *xyz, size_t groups, int k, int C,

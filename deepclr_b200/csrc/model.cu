@@ -194,13 +194,22 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     }
     timing_mark(m, ST_TAIL, 0, st);
     // fully connected tail: helper.py:97-123 (ReLU after both), final nn.Linear, activation deepclr.py:275-282
-    DCLR_TRY(linear_f32_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
-                               a.out_linear[1], a.out_linear[0], 1, st));
-    DCLR_TRY(linear_f32_launch(m->t1, a.out_linear[1], m->lin[1].W, m->lin[1].b, m->t2, a.out_linear[2], B,
-                               a.out_linear[2], a.out_linear[1], 1, st));
-    DCLR_TRY(linear_f32_launch(m->t2, a.out_linear[2], m->fin.W, m->fin.b, y_out, m->label_dim, B, m->label_dim,
-                               a.out_linear[2], 0, st));
-    DCLR_TRY(pose_activation_launch(y_out, B, m->label_dim, a.label_type, st));
+    if (a.out_linear[0] % 4 == 0 && a.out_linear[1] % 4 == 0 && a.out_linear[2] % 4 == 0) {
+        DCLR_TRY(linear_skinny_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
+                                      a.out_linear[1], a.out_linear[0], 1, 0, st));
+        DCLR_TRY(linear_skinny_launch(m->t1, a.out_linear[1], m->lin[1].W, m->lin[1].b, m->t2, a.out_linear[2], B,
+                                      a.out_linear[2], a.out_linear[1], 1, 0, st));
+        DCLR_TRY(linear_skinny_launch(m->t2, a.out_linear[2], m->fin.W, m->fin.b, y_out, m->label_dim, B,
+                                      m->label_dim, a.out_linear[2], 2, a.label_type, st));
+    } else {
+        DCLR_TRY(linear_f32_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
+                                   a.out_linear[1], a.out_linear[0], 1, st));
+        DCLR_TRY(linear_f32_launch(m->t1, a.out_linear[1], m->lin[1].W, m->lin[1].b, m->t2, a.out_linear[2], B,
+                                   a.out_linear[2], a.out_linear[1], 1, st));
+        DCLR_TRY(linear_f32_launch(m->t2, a.out_linear[2], m->fin.W, m->fin.b, y_out, m->label_dim, B, m->label_dim,
+                                   a.out_linear[2], 0, st));
+        DCLR_TRY(pose_activation_launch(y_out, B, m->label_dim, a.label_type, st));
+    }
     timing_mark(m, ST_TAIL, 1, st);
     if (motion_out) {
         StageScope sc(m, ST_LAYOUT, st);

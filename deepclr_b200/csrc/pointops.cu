@@ -282,10 +282,133 @@ knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int
     }
 }
 
+// Fast path for Nx <= 1024, k <= 32 (the model's shapes: queries and candidates are the FPS samples).  A warp owns
+// a query; lane l holds the squared distances to candidates l, l+32, ... in registers.  Instead of extracting the k
+// minima from all Nx keys, a threshold T = k-th smallest of the 32 per-lane minima is taken first: at least k
+// candidates have d <= T (one per contributing lane), typically ~1.5k do.  Those few are compacted to shared memory
+// as (d bits << 32 | index) keys and the k ordered minima are extracted from at most 4 keys per lane.  Ordering by
+// the packed key is "ascending d^2, ties -> lower index", the same order as knn_kernel / the oracle.
+constexpr int KNNF_WARPS = 8;
+constexpr int KNNF_QPW = 4;                 // queries per warp (share the staged candidates)
+constexpr int KNNF_CAP = 128;               // compacted candidates per query
+
+template <int KPL>
+__global__ void __launch_bounds__(KNNF_WARPS * 32)
+knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
+                int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local) {
+    __shared__ float s_x[KPL * 32], s_y[KPL * 32], s_z[KPL * 32];
+    __shared__ uint64_t s_cand[KNNF_WARPS][KNNF_CAP];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y;
+    const float *xb = x + (size_t)b * Nx * 3;
+    for (int j = tid; j < KPL * 32; j += KNNF_WARPS * 32) {
+        const bool ok = j < Nx;
+        s_x[j] = ok ? __ldg(xb + j * 3) : 0.f;
+        s_y[j] = ok ? __ldg(xb + j * 3 + 1) : 0.f;
+        s_z[j] = ok ? __ldg(xb + j * 3 + 2) : 0.f;
+    }
+    __syncthreads();
+    const uint64_t KMAX = ~0ull;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    for (int qi = 0; qi < KNNF_QPW; ++qi) {
+        const int q = (blockIdx.x * KNNF_WARPS + warp) * KNNF_QPW + qi;
+        if (q >= Ny) break;                                     // warp-uniform
+        const size_t gy = (size_t)b * Ny + q;
+        const float qx = __ldg(y + gy * 3), qy = __ldg(y + gy * 3 + 1), qz = __ldg(y + gy * 3 + 2);
+        float d[KPL];
+        float lmin = INFINITY;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) {
+            const int j = i * 32 + lane;
+            // torch-cluster: tmp_dist += (x - y)^2 per dimension, x = candidate, y = query
+            const float v = sqdist_tc(s_x[j] - qx, s_y[j] - qy, s_z[j] - qz);
+            d[i] = j < Nx ? v : INFINITY;
+            lmin = fminf(lmin, d[i]);
+        }
+        // threshold: k rounds of "take the smallest remaining lane minimum" (d >= 0, so its bit image is ordered)
+        uint32_t v = __float_as_uint(lmin), T = 0;
+        for (int r = 0; r < k; ++r) {
+            T = __reduce_min_sync(0xffffffffu, v);
+            if (v == T) v = 0xffffffffu;
+        }
+        // count + compact everything with d <= T
+        int cnt = 0;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) cnt += (__float_as_uint(d[i]) <= T) ? 1 : 0;
+        int off = cnt;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, off, s);
+            if (lane >= s) off += o;
+        }
+        const int total = __shfl_sync(0xffffffffu, off, 31);
+        off -= cnt;
+        uint64_t *cand = s_cand[warp];
+        uint64_t c0 = KMAX, c1 = KMAX, c2 = KMAX, c3 = KMAX;
+        const bool fits = total <= KNNF_CAP;                    // warp-uniform
+        __syncwarp();
+        if (fits) {
+#pragma unroll
+            for (int i = 0; i < KPL; ++i)
+                if (__float_as_uint(d[i]) <= T)
+                    cand[off++] = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(i * 32 + lane);
+            __syncwarp();
+            c0 = lane < total ? cand[lane] : KMAX;
+            c1 = lane + 32 < total ? cand[lane + 32] : KMAX;
+            c2 = lane + 64 < total ? cand[lane + 64] : KMAX;
+            c3 = lane + 96 < total ? cand[lane + 96] : KMAX;
+        }
+        (void)lt_mask;
+        const size_t o0 = gy * k;
+        for (int r = 0; r < k; ++r) {
+            uint64_t lm;
+            if (fits) {
+                lm = c0 < c1 ? c0 : c1;
+                const uint64_t t2 = c2 < c3 ? c2 : c3;
+                lm = lm < t2 ? lm : t2;
+            } else {                                            // rare: rescan the full register set
+                lm = KMAX;
+#pragma unroll
+                for (int i = 0; i < KPL; ++i) {
+                    const uint64_t key = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(i * 32 + lane);
+                    lm = (d[i] != INFINITY && key < lm) ? key : lm;
+                }
+            }
+            const uint64_t win = warp_min_u64(lm);
+            if (lm == win) {                                    // exactly one lane: indices are unique
+                if (fits) {
+                    c0 = c0 == win ? KMAX : c0; c1 = c1 == win ? KMAX : c1;
+                    c2 = c2 == win ? KMAX : c2; c3 = c3 == win ? KMAX : c3;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < KPL; ++i)
+                        if ((uint32_t)win == (uint32_t)(i * 32 + lane)) d[i] = INFINITY;
+                }
+            }
+            if (lane == 0) {
+                const uint32_t ci = (uint32_t)win;
+                if (row_out) row_out[o0 + r] = (int64_t)gy;
+                if (col_out) col_out[o0 + r] = (int64_t)((size_t)b * Nx + ci);
+                if (col_local) col_local[o0 + r] = (int32_t)ci;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
                int32_t *col_local, cudaStream_t st) {
-    knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
-    DCLR_LAUNCH_CHECK("knn_kernel");
+    const dim3 fgrid(div_up(Ny, KNNF_WARPS * KNNF_QPW), B);
+    if (k <= 32 && Nx <= 512) {
+        knn_fast_kernel<16><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        DCLR_LAUNCH_CHECK("knn_fast_kernel");
+    } else if (k <= 32 && Nx <= 1024) {
+        knn_fast_kernel<32><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        DCLR_LAUNCH_CHECK("knn_fast_kernel");
+    } else {
+        knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        DCLR_LAUNCH_CHECK("knn_kernel");
+    }
     return DCLR_OK;
 }
 
