@@ -10,6 +10,7 @@
 //     next = argmax_k t_k         ties -> LOWEST point index (BASELINE.json's stated rule)
 #include "common.cuh"
 #include "kernels.cuh"
+#include "ptx.cuh"
 #include <limits.h>
 
 namespace dclr {
@@ -47,28 +48,37 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
     return r;
 }
 
-// T threads, PP point PAIRS per thread: thread tid owns points 2*(tid + i*T) and 2*(tid + i*T) + 1, i < PP.
-// ZS: read z from shared memory (one 8-byte load per pair) instead of registers -- needed at T=1024, PP=8 where only
-// 64 registers per thread exist.  One __syncthreads per round: every warp publishes (max, lowest index at max) into
-// a parity-double-buffered slot, then every warp reduces the <= 32 slots redundantly.
+__device__ __forceinline__ uint64_t lds64(uint32_t addr) {
+    uint64_t r;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(r) : "r"(addr));
+    return r;
+}
+
+// T threads, PP point PAIRS per thread: thread tid owns points 2*(tid + i*T) and 2*(tid + i*T) + 1, i < PP.  The
+// shared arrays are padded to the full capacity CAP = 2*T*PP so that no load needs a bounds guard (the padding never
+// wins: its running minimum starts at -1).  ZS: read z from shared memory (one 8-byte load per pair, immediate
+// offsets) instead of registers -- needed at T=1024, PP=8 where only 64 registers per thread exist.
+// Per round: packed distance update -> warp redux max -> slot per warp -> barrier -> block max; only the thread(s)
+// holding the block max look up their lowest index and atomicMin it -> barrier.
 template <int T, int PP, bool ZS>
 __global__ void __launch_bounds__(T, 1)
 fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int32_t *__restrict__ idx_out,
                     float *__restrict__ new_xyz_out) {
     extern __shared__ __align__(16) float smem[];
-    const int NP = (N + 1) & ~1;                                   // even padded length
-    float *s_x = smem, *s_y = smem + NP, *s_z = smem + 2 * NP;
-    int2 *s_res = reinterpret_cast<int2 *>(smem + 3 * NP);          // [2][32]
+    constexpr int CAP = 2 * T * PP;
+    constexpr int NW = T / 32;
+    float *s_x = smem, *s_y = smem + CAP, *s_z = smem + 2 * CAP;
+    int *s_wmax = reinterpret_cast<int *>(smem + 3 * CAP);          // [2][32]
+    int *s_win = s_wmax + 64;                                       // [2]
 
     const int b = blockIdx.x;
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
-    constexpr int NW = T / 32;
     pts += (size_t)b * N * stride;
     idx_out += (size_t)b * npoint;
     if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
 
-    // stage the cloud: coalesced (float4 when the point stride is 4 floats)
+    // stage the cloud: coalesced (float4 when the point stride is 4 floats); zero the padding
     if (stride == 4) {
         const float4 *p4 = reinterpret_cast<const float4 *>(pts);
         for (int k = tid; k < N; k += T) {
@@ -81,18 +91,19 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
             s_x[k] = __ldg(p); s_y[k] = __ldg(p + 1); s_z[k] = __ldg(p + 2);
         }
     }
-    if (tid == 0 && NP > N) { s_x[N] = 0.f; s_y[N] = 0.f; s_z[N] = 0.f; }
+    for (int k = N + tid; k < CAP; k += T) { s_x[k] = 0.f; s_y[k] = 0.f; s_z[k] = 0.f; }
+    if (tid < 2) s_win[tid] = INT_MAX;
     __syncthreads();
 
     uint64_t x2[PP], y2[PP], z2[ZS ? 1 : PP];
     float tl[PP], th[PP];
+    const uint32_t zaddr = ptx::smem_u32(s_z) + tid * 8;
 #pragma unroll
     for (int i = 0; i < PP; ++i) {
         const int k = 2 * (tid + i * T);
-        const bool ok = k < NP;                                   // NP even: the pair is inside the padded arrays
-        x2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_x + k) : 0ull;
-        y2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_y + k) : 0ull;
-        if (!ZS) z2[i] = ok ? *reinterpret_cast<const uint64_t *>(s_z + k) : 0ull;
+        x2[i] = *reinterpret_cast<const uint64_t *>(s_x + k);
+        y2[i] = *reinterpret_cast<const uint64_t *>(s_y + k);
+        if (!ZS) z2[i] = *reinterpret_cast<const uint64_t *>(s_z + k);
         tl[i] = k < N ? 1e10f : -1.0f;        // -1 can never win (reference: best starts at -1, strict >)
         th[i] = k + 1 < N ? 1e10f : -1.0f;
     }
@@ -108,13 +119,7 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
         float best = -1.0f;
 #pragma unroll
         for (int i = 0; i < PP; ++i) {
-            uint64_t zz;
-            if (ZS) {
-                const int k = 2 * (tid + i * T);
-                zz = *reinterpret_cast<const uint64_t *>(s_z + (k < NP ? k : 0));
-            } else {
-                zz = z2[i];
-            }
+            const uint64_t zz = ZS ? lds64(zaddr + i * (T * 8)) : z2[i];
             const uint64_t dx = sub2(x2[i], xo), dy = sub2(y2[i], yo), dz = sub2(zz, zo);
             const uint64_t d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
             float dl, dh;
@@ -123,25 +128,26 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
             th[i] = fminf(dh, th[i]);
             best = max3(best, tl[i], th[i]);
         }
-        // warp: max value (through its integer image; -1.0f is a negative int) and the lowest index holding it
+        // block max of the float through its integer image (values are >= 0 or exactly -1.0f, a negative int)
         const int bi = __float_as_int(best);
         const int wm = __reduce_max_sync(0xffffffffu, bi);
-        int cand = INT_MAX;
-        if (bi == wm) {
+        const int par = j & 1;
+        if (lane == 0) s_wmax[par * 32 + warp] = wm;
+        __syncthreads();
+        const int m = __reduce_max_sync(0xffffffffu, lane < NW ? s_wmax[par * 32 + lane] : INT_MIN);
+        if (tid == 0) s_win[par ^ 1] = INT_MAX;                  // re-arm the other slot for the next round
+        if (bi == m) {
+            int cand = INT_MAX;
 #pragma unroll
             for (int i = PP - 1; i >= 0; --i) {                  // descending: the lowest index survives
                 const int k = 2 * (tid + i * T);
-                cand = __float_as_int(th[i]) == wm ? k + 1 : cand;
-                cand = __float_as_int(tl[i]) == wm ? k : cand;
+                cand = __float_as_int(th[i]) == m ? k + 1 : cand;
+                cand = __float_as_int(tl[i]) == m ? k : cand;
             }
+            atomicMin(&s_win[par], cand);
         }
-        const int wi = __reduce_min_sync(0xffffffffu, cand);
-        int2 *slot = s_res + (j & 1) * 32;
-        if (lane == 0) slot[warp] = make_int2(wm, wi);
         __syncthreads();
-        const int2 e = lane < NW ? slot[lane] : make_int2(INT_MIN, INT_MAX);
-        const int m = __reduce_max_sync(0xffffffffu, e.x);
-        old = __reduce_min_sync(0xffffffffu, e.x == m ? e.y : INT_MAX);
+        old = s_win[par];
         if (tid == 0) idx_out[j] = old;
     }
     if (tid == 0 && new_xyz_out && npoint > 0) {
@@ -201,7 +207,7 @@ fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, 
 template <int T, int PP, bool ZS>
 static int launch_resident(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx,
                            cudaStream_t st) {
-    size_t smem = (size_t)3 * ((N + 1) & ~1) * sizeof(float) + 64 * sizeof(int2);
+    size_t smem = (size_t)3 * (2 * T * PP) * sizeof(float) + 66 * sizeof(int);
     auto kern = fps_resident_kernel<T, PP, ZS>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<B, T, smem, st>>>(pts, stride, N, npoint, idx, nx);
