@@ -14,6 +14,12 @@ int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *
 int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
                       const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad,
                       cudaStream_t st);
+// ballgrid.cu: grid-accelerated ball query for large clouds; *used = 0 when the shape is not handled (then call
+// ball_query_launch).  ws must hold ball_grid_workspace_bytes(B, N) bytes.
+size_t ball_grid_workspace_bytes(int B, int N);
+int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
+                     const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad, void *ws,
+                     cudaStream_t st, int *used);
 int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
                int32_t *col_local, cudaStream_t st);
 

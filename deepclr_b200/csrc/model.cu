@@ -21,6 +21,7 @@ struct dclr_model {
     int last_launches = 0;
     // carved pointers (valid after ensure_ws)
     int32_t *fps_idx, *bq_idx[2], *bq_cnt[2], *knn_col;
+    void *bq_ws;
     float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
     uint8_t *mask;
     dclr::TcModel *tc = nullptr;     // bf16 tensor-core path (mlp_tc.cu)
@@ -53,6 +54,7 @@ static size_t carve(dclr_model *m, char *base, int G, int N, int B) {
     }
     m->sa_feat = (float *)take((size_t)G * M * m->F * 4);
     m->fps_temp = (float *)take(N > 16384 ? (size_t)G * N * 4 : 0);
+    m->bq_ws = take(ball_grid_workspace_bytes(G, N));
     const size_t BM = (size_t)B * M;
     const size_t R = BM * (a.knn_k > 0 ? a.knn_k : 1);
     m->knn_col = (int32_t *)take(R * 4);
@@ -132,8 +134,13 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     }
     {
         StageScope sc(m, ST_BALL, st);
-        DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
-                                   m->bq_idx, m->bq_cnt, /*pad=*/0, st));
+        int used = 0;
+        DCLR_TRY(ball_grid_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
+                                  m->bq_idx, m->bq_cnt, /*pad=*/0, m->bq_ws, st, &used));
+        if (used) ++m->last_launches;                      // build + query
+        else
+            DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
+                                       m->bq_idx, m->bq_cnt, /*pad=*/0, st));
     }
     StageScope sc(m, ST_SA, st);
     SaArgs s;

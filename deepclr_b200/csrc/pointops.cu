@@ -449,6 +449,15 @@ extern "C" int dclr_ball_query(const float *new_xyz, const float *pts, int pt_st
     if (B == 0 || M == 0) return DCLR_OK;
     int32_t *idx[1] = {idx_out};
     int32_t *cnt[1] = {cnt_out};
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N >= 2048) {                                       // large clouds: uniform-grid candidate pruning (ballgrid.cu)
+        void *ws = nullptr;
+        DCLR_CUDA(cudaMallocAsync(&ws, ball_grid_workspace_bytes(B, N), st));
+        int used = 0;
+        int rc = ball_grid_launch(new_xyz, pts, pt_stride, B, N, M, 1, &radius, &nsample, idx, cnt, pad, ws, st, &used);
+        cudaFreeAsync(ws, st);
+        if (rc != DCLR_OK || used) return rc;
+    }
     return ball_query_launch(new_xyz, pts, pt_stride, B, N, M, 1, &radius, &nsample, idx, cnt, pad,
                              (cudaStream_t)stream);
 }

@@ -85,6 +85,25 @@ def test_ball_query_matches_oracle(p2, B, N, M, r, ns):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize('N,M,r,ns', [(16384, 1024, 0.5, 512), (16384, 1024, 1.0, 1024), (40000, 500, 2.5, 64),
+                                      (131072, 256, 0.7, 32)])
+def test_ball_query_grid_path_lidar_and_clustered(p2, N, M, r, ns):
+    """Large clouds go through the uniform-grid kernels (ballgrid.cu): KITTI-shaped scans (dense rings near the sensor,
+    sparse far away), a degenerate cloud with most points in one cell, and centres outside the bounding box."""
+    from deepclr_b200 import synth
+    rng = np.random.default_rng(N + ns)
+    lidar = synth._lidar_scan(np.random.Generator(np.random.PCG64(7)), N)[0].astype(np.float32)
+    clustered = rng.normal(0, 0.3, (N, 3)).astype(np.float32)
+    clustered[: N // 8] = rng.uniform(-50, 50, (N // 8, 3)).astype(np.float32)
+    xyz = np.stack([lidar, clustered])
+    new_xyz = xyz[:, rng.permutation(N)[:M]].copy()
+    new_xyz[0, 0] = (500.0, -500.0, 3.0)                     # outside the box: empty
+    new_xyz[1, 1] = xyz[1].max(0) + 0.5 * r                  # just outside a corner
+    want = ops.ball_query(r, ns, xyz, new_xyz)
+    got = p2.ball_query(r, ns, _t(xyz), _t(new_xyz)).cpu().numpy()
+    assert np.array_equal(got, want)
+
+
 def test_ball_query_stride4_two_radii_compact():
     from deepclr_b200 import _lib
     rng = np.random.default_rng(9)
