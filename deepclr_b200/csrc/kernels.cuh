@@ -30,7 +30,8 @@ struct SaArgs {
     const int32_t *idx[2];   // compact neighbour lists [B,M,ns]
     const int32_t *cnt[2];   // [B,M]
     int ns[2];
-    const float *w[2];       // per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
+    const float *w_host[2];  // HOST copies, per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
+                             // (they travel in the kernel parameter block = constant bank)
     float *out;              // [B,M,ld_out] point-major; scale s writes columns [s*H3, (s+1)*H3)
     int N, M, ld_out, nscales;
 };

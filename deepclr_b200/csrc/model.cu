@@ -11,7 +11,7 @@ struct dclr_model {
     int label_dim, F, nmerge_in, head_in;
     float *d_w = nullptr;            // all parameters, state-dict order
     size_t n_w = 0;
-    const float *sa_w[2] = {nullptr, nullptr};
+    std::vector<float> sa_w_host[2];   // SA MLP parameters, host copy (passed as kernel parameters)
     struct Lin { const float *W, *b; int out, in; };
     Lin merge[3], outc[5], lin[2], fin;
     int numerics = 0;
@@ -148,7 +148,7 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     s.out = m->sa_feat;
     for (int i = 0; i < 2; ++i) {
         s.idx[i] = m->bq_idx[i]; s.cnt[i] = m->bq_cnt[i]; s.ns[i] = a.nsamples[i < a.num_scales ? i : 0];
-        s.w[i] = m->sa_w[i];
+        s.w_host[i] = m->sa_w_host[i < a.num_scales ? i : 0].data();
     }
     DCLR_TRY(sa_mlp_launch(s, G, a.input_dim, a.sa_mlp[0], st));
     return DCLR_OK;
@@ -279,7 +279,10 @@ extern "C" int dclr_model_create(const dclr_arch *arch, const float *weights, si
         return fail(DCLR_E_CUDA, "dclr_model_create: %s", cudaGetErrorString(e));
     }
     m->n_w = off;
-    for (int s = 0; s < a.num_scales; ++s) m->sa_w[s] = m->d_w + sa_off[s];
+    for (int s = 0; s < a.num_scales; ++s) {
+        const size_t end = s + 1 < a.num_scales ? sa_off[s + 1] : w_off[first_dense];
+        m->sa_w_host[s].assign(weights + sa_off[s], weights + end);
+    }
     size_t q = first_dense;
     auto lin = [&](int o, int i) { dclr_model::Lin L{m->d_w + w_off[q], m->d_w + b_off[q], o, i}; ++q; return L; };
     cin = m->nmerge_in;
