@@ -127,9 +127,9 @@ __device__ __forceinline__ void store_coord_chunks(uint32_t addr0, uint32_t addr
 // Hidden-layer epilogue of one thread (= one tile row): TMEM accumulators [ncols] -> +bias, ReLU -> 16-bit ->
 // the row's 16-byte vectors of the next layer's A/B operand tile.  taddr already contains the warp's lane offset.
 template <typename T16>
-__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int ncols, const float *__restrict__ bias_s,
-                                                uint32_t act_row_addr) {
-    for (int c0 = 0; c0 < ncols; c0 += 32) {
+__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int c_begin, int c_end,
+                                                const float *__restrict__ bias_s, uint32_t act_row_addr) {
+    for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         uint32_t v[32];
         ptx::tmem_ld32(taddr + c0, v);
         ptx::tmem_ld_wait();
@@ -148,6 +148,33 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int ncols, const
     }
 }
 
+// Last flow layer (transposed): this thread's TMEM lane is one output channel, the 128 columns are the tile rows
+// (groups of k neighbours).  Radius-masked max per group, + bias, ReLU, store.  KC > 0: k known at compile time, the
+// group bookkeeping folds away and the per-group maxima become independent chains.
+template <int KC>
+__device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&mk)[4], int k_rt, int g, int nvalid,
+                                               float bias, float *__restrict__ out, int ld) {
+    const int k = KC ? KC : k_rt;
+    float cur = -INFINITY;
+    int cnt = 0, og = 0;
+#pragma unroll
+    for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        ptx::tmem_ld32(taddr + c0, v);
+        ptx::tmem_ld_wait();
+        const uint32_t mword = mk[c0 >> 5];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const float x = ((mword >> i) & 1u) ? -INFINITY : __uint_as_float(v[i]);
+            cur = fmaxf(cur, x);
+            if (++cnt == k) {
+                if (og < g && og < nvalid) out[(size_t)og * ld] = fmaxf(cur + bias, 0.f);
+                ++og; cnt = 0; cur = -INFINITY;
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- flow embedding
 struct FlowArgs {
     const float *xyz;       // [2B, n, 3] sampled coordinates, templates first
@@ -162,7 +189,9 @@ struct FlowArgs {
 };
 
 constexpr int FLOW_SLOTS = 2;
-constexpr int FLOW_THREADS = (FLOW_SLOTS * 4 + 1) * 32;
+constexpr int FLOW_WPS = 8;           // build/epilogue warps per slot: 4 TMEM lane quarters x 2 column halves
+constexpr int FLOW_MMA_WARP = FLOW_SLOTS * FLOW_WPS;
+constexpr int FLOW_THREADS = (FLOW_MMA_WARP + 1) * 32;
 
 template <typename T16>
 __global__ void __launch_bounds__(FLOW_THREADS, 1)
@@ -183,12 +212,12 @@ flow_tc_kernel(FlowArgs a) {
     if (tid == 0) {
         ptx::mbar_init(wbar, 1);
         for (int s = 0; s < FLOW_SLOTS; ++s) {
-            ptx::mbar_init(&ready[s], 128);
+            ptx::mbar_init(&ready[s], FLOW_WPS * 32);
             ptx::mbar_init(&done[s], 1);
         }
         ptx::fence_mbar_init();
     }
-    if (warp == FLOW_SLOTS * 4) ptx::tmem_alloc(s_tmem, 512);
+    if (warp == FLOW_MMA_WARP) ptx::tmem_alloc(s_tmem, 512);
     for (int e = tid; e < 256 + H3; e += FLOW_THREADS) s_bias[e] = __ldg(a.bias + e);
     ptx::tc_fence_before();
     __syncthreads();
@@ -197,7 +226,7 @@ flow_tc_kernel(FlowArgs a) {
     const int tiles_per_iter = gridDim.x * FLOW_SLOTS;
     constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
 
-    if (warp == FLOW_SLOTS * 4) {
+    if (warp == FLOW_MMA_WARP) {
         // ===================== weight load (once) + MMA issue =====================
         if (lane == 0) {
             ptx::mbar_expect_tx(wbar, w1_bytes + w2_bytes + w3_bytes);
@@ -241,62 +270,80 @@ flow_tc_kernel(FlowArgs a) {
             }
         }
     } else {
-        // ===================== row build + epilogues (4 warps per slot) =====================
-        const int s = warp >> 2, q = warp & 3;
+        // ===================== row build + epilogues (8 warps per slot) =====================
+        // warp = (slot, column half, lane quarter): both halves of a quarter own the same 32 tile rows / TMEM lanes and
+        // split the columns (hidden layers), the operand chunks (row build) and the 128-channel blocks (last layer).
+        const int s = warp / FLOW_WPS, half = (warp % FLOW_WPS) >> 2, q = warp & 3;
         const int r = q * 32 + lane;                                   // tile row == TMEM lane
         const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
         const uint32_t act_row = act + r * 16;
         const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + s * 256;
         const int k = a.k, n = a.n, F = a.F, g = a.groups_per_tile;
+        const int fc = F / 8;                                          // chunks per feature block
         uint32_t dphase = 0;
         for (int tile = blockIdx.x * FLOW_SLOTS + s; tile < a.num_tiles; tile += tiles_per_iter) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * g;
-            // ---- build row r = (point p0 + r / k, neighbour r % k): [f_tmpl | f_src | dp | 0]
+            // ---- build row r = (point p0 + r / k, neighbour r % k): [f_tmpl | f_src | dp hi,hi,lo | 0]
             const int grp = r / k, j = r - grp * k;
             const int pt = p0 + grp;
             const bool valid = grp < g && pt < n;
-            bool masked = true;
+            bool masked = true;                                        // rows that do not exist never contribute
             if (valid) {
                 const size_t trow = (size_t)b * n + pt;
                 const int src = __ldg(a.nbr + trow * k + j);
                 const size_t srow = (size_t)(a.B + b) * n + src;
-                const float4 *ft = reinterpret_cast<const float4 *>(a.feat + trow * F);
-                const float4 *fs = reinterpret_cast<const float4 *>(a.feat + srow * F);
+                if (half == 0) {
+                    const float4 *ft = reinterpret_cast<const float4 *>(a.feat + trow * F);
 #pragma unroll 4
-                for (int c = 0; c < F / 8; ++c) {
-                    const float4 u0 = __ldg(ft + 2 * c), u1 = __ldg(ft + 2 * c + 1);
-                    const float4 v0 = __ldg(fs + 2 * c), v1 = __ldg(fs + 2 * c + 1);
-                    st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
-                                 Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
-                    st_shared_v4(act_row + (F / 8 + c) * TC_LBO, Cvt<T16>::pack(v0.x, v0.y),
-                                 Cvt<T16>::pack(v0.z, v0.w), Cvt<T16>::pack(v1.x, v1.y), Cvt<T16>::pack(v1.z, v1.w));
+                    for (int c = 0; c < fc; ++c) {
+                        const float4 u0 = __ldg(ft + 2 * c), u1 = __ldg(ft + 2 * c + 1);
+                        st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
+                                     Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
+                    }
+                    const float *pt3 = a.xyz + trow * 3, *ps3 = a.xyz + srow * 3;
+                    const float dx = __ldg(ps3) - __ldg(pt3), dy = __ldg(ps3 + 1) - __ldg(pt3 + 1),
+                                dz = __ldg(ps3 + 2) - __ldg(pt3 + 2);
+                    store_coord_chunks<T16>(act_row + (2 * fc) * TC_LBO, act_row + (2 * fc + 1) * TC_LBO, dx, dy, dz);
+                    // radius mask in fp32 on the raw displacement (deepclr.py:220-222)
+                    masked = a.radius > 0.f && sqrtf(dx * dx + dy * dy + dz * dz) >= a.radius;
+                } else {
+                    const float4 *fs = reinterpret_cast<const float4 *>(a.feat + srow * F);
+#pragma unroll 4
+                    for (int c = 0; c < fc; ++c) {
+                        const float4 v0 = __ldg(fs + 2 * c), v1 = __ldg(fs + 2 * c + 1);
+                        st_shared_v4(act_row + (fc + c) * TC_LBO, Cvt<T16>::pack(v0.x, v0.y),
+                                     Cvt<T16>::pack(v0.z, v0.w), Cvt<T16>::pack(v1.x, v1.y), Cvt<T16>::pack(v1.z, v1.w));
+                    }
+                    for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
                 }
-                const float *pt3 = a.xyz + trow * 3, *ps3 = a.xyz + srow * 3;
-                const float dx = __ldg(ps3) - __ldg(pt3), dy = __ldg(ps3 + 1) - __ldg(pt3 + 1),
-                            dz = __ldg(ps3 + 2) - __ldg(pt3 + 2);
-                store_coord_chunks<T16>(act_row + (2 * F / 8) * TC_LBO, act_row + (2 * F / 8 + 1) * TC_LBO, dx, dy, dz);
-                for (int c = 2 * F / 8 + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
-                // radius mask in fp32 on the raw displacement (deepclr.py:220-222)
-                masked = a.radius > 0.f && sqrtf(dx * dx + dy * dy + dz * dz) >= a.radius;
             } else {
-                for (int c = 0; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                const int cb = half == 0 ? 0 : fc, ce = half == 0 ? fc : 2 * fc;
+                for (int c = cb; c < ce; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                if (half == 0) {
+                    st_shared_v4(act_row + (2 * fc) * TC_LBO, 0u, 0u, 0u, 0u);
+                    st_shared_v4(act_row + (2 * fc + 1) * TC_LBO, 0u, 0u, 0u, 0u);
+                } else {
+                    for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                }
             }
-            const uint32_t mw = __ballot_sync(0xffffffffu, masked);
-            if (lane == 0) s_maskw[s * 4 + q] = mw;
+            if (half == 0) {                                           // warp-uniform
+                const uint32_t mw = __ballot_sync(0xffffffffu, masked);
+                if (lane == 0) s_maskw[s * 4 + q] = mw;
+            }
             ptx::fence_proxy_async_smem();
             ptx::mbar_arrive(&ready[s]);
             // ---- layer 1 epilogue -> H1 (in place of the rows)
             ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
             ptx::tc_fence_after();
-            epilogue_hidden<T16>(tlane, 128, s_bias, act_row);
+            epilogue_hidden<T16>(tlane, half * 64, half * 64 + 64, s_bias, act_row);
             ptx::tc_fence_before();
             ptx::fence_proxy_async_smem();
             ptx::mbar_arrive(&ready[s]);
             // ---- layer 2 epilogue -> H2
             ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
             ptx::tc_fence_after();
-            epilogue_hidden<T16>(tlane + 128, 128, s_bias + 128, act_row);
+            epilogue_hidden<T16>(tlane + 128, half * 64, half * 64 + 64, s_bias + 128, act_row);
             ptx::tc_fence_before();
             ptx::fence_proxy_async_smem();
             ptx::mbar_arrive(&ready[s]);
@@ -306,33 +353,20 @@ flow_tc_kernel(FlowArgs a) {
             uint32_t mk[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) mk[i] = s_maskw[s * 4 + i];
-            for (int mb = 0; mb < H3 / 128; ++mb) {
+            for (int mb = half; mb < H3 / 128; mb += 2) {
                 const int ch = mb * 128 + r;
                 const float bias = s_bias[256 + ch];
-                float cur = -INFINITY;
-                int cnt = 0, og = 0;
-#pragma unroll
-                for (int c0 = 0; c0 < 128; c0 += 32) {
-                    uint32_t v[32];
-                    ptx::tmem_ld32(tlane + mb * 128 + c0, v);
-                    ptx::tmem_ld_wait();
-                    const uint32_t mword = mk[c0 >> 5];
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if (!((mword >> i) & 1u)) cur = fmaxf(cur, __uint_as_float(v[i]));
-                        if (++cnt == k) {
-                            if (og < g && p0 + og < n)
-                                a.out[((size_t)b * n + p0 + og) * H3 + ch] = fmaxf(cur + bias, 0.f);
-                            ++og; cnt = 0; cur = -INFINITY;
-                        }
-                    }
-                }
+                float *out = a.out + ((size_t)b * n + p0) * H3 + ch;
+                const uint32_t ta = tlane + mb * 128;
+                if (k == 20) flow_group_max<20>(ta, mk, k, g, n - p0, bias, out, H3);
+                else if (k == 30) flow_group_max<30>(ta, mk, k, g, n - p0, bias, out, H3);
+                else flow_group_max<0>(ta, mk, k, g, n - p0, bias, out, H3);
             }
             ptx::tc_fence_before();
         }
     }
     __syncthreads();
-    if (warp == FLOW_SLOTS * 4) ptx::tmem_dealloc(tmem_base, 512);
+    if (warp == FLOW_MMA_WARP) ptx::tmem_dealloc(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------- output head
@@ -340,7 +374,9 @@ constexpr int HEAD_LAYERS = 5;
 constexpr int HEAD_KT = 64;                      // K elements per streamed weight tile (128 rows x 64 = 16 KB)
 constexpr int HEAD_STAGES = 5;
 constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
-constexpr int HEAD_THREADS = 6 * 32;             // 4 epilogue warps, 1 weight-producer warp, 1 MMA warp
+constexpr int HEAD_EPI_WARPS = 8;                // 4 TMEM lane quarters x 2 column halves
+constexpr int HEAD_PROD_WARP = HEAD_EPI_WARPS, HEAD_MMA_WARP = HEAD_EPI_WARPS + 1;
+constexpr int HEAD_THREADS = (HEAD_EPI_WARPS + 2) * 32;
 
 struct HeadArgs {
     const float *feat;      // [B*n, C0] motion features
@@ -371,12 +407,12 @@ head_tc_kernel(HeadArgs a) {
 
     if (tid == 0) {
         for (int i = 0; i < HEAD_STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
-        ptx::mbar_init(act_ready, 128);
+        ptx::mbar_init(act_ready, HEAD_EPI_WARPS * 32);
         ptx::mbar_init(layer_done, 1);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&fin_done[i], 1); ptx::mbar_init(&fin_free[i], 128); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&fin_done[i], 1); ptx::mbar_init(&fin_free[i], HEAD_EPI_WARPS * 32); }
         ptx::fence_mbar_init();
     }
-    if (warp == 5) ptx::tmem_alloc(s_tmem, 512);
+    if (warp == HEAD_MMA_WARP) ptx::tmem_alloc(s_tmem, 512);
     for (int e = tid; e < nbias; e += HEAD_THREADS) s_bias[e] = __ldg(a.bias + e);
     ptx::tc_fence_before();
     __syncthreads();
@@ -384,7 +420,7 @@ head_tc_kernel(HeadArgs a) {
     const uint32_t tmem_base = *s_tmem;
     constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
 
-    if (warp == 4) {
+    if (warp == HEAD_PROD_WARP) {
         // ===================== weight producer: stream every tile of every layer, once per row tile ============
         if (lane == 0) {
             uint32_t it = 0;
@@ -402,7 +438,7 @@ head_tc_kernel(HeadArgs a) {
                         }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == HEAD_MMA_WARP) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t act = ptx::smem_u32(s_act), wt = ptx::smem_u32(s_wt);
@@ -445,31 +481,40 @@ head_tc_kernel(HeadArgs a) {
         }
     } else {
         // ===================== row build + epilogues =====================
-        const int r = warp * 32 + lane;
+        // warp = (column half, lane quarter): both halves own the same 32 rows / TMEM lanes and split the columns
+        const int half = warp >> 2, q = warp & 3;
+        const int r = q * 32 + lane;
         const uint32_t act_row = ptx::smem_u32(s_act) + r * 16;
-        const uint32_t tlane = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
         uint32_t n_done = 0, fin_cnt[2] = {0, 0};
         const int C0 = a.C0, n = a.n;
+        const int cc = C0 / 8, cmid = cc / 2, kc0 = a.Kp[0] / 8;
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * 128;
             const int pt = p0 + r;
-            // ---- input rows: [motion feat (C0) | xyz (3) | 0]
+            // ---- input rows: [motion feat (C0) | xyz hi,hi,lo | 0]; half 0 writes the first feature chunks, half 1
+            //      the rest, the coordinates and the padding
+            const int cb = half == 0 ? 0 : cmid, ce = half == 0 ? cmid : cc;
             if (pt < n) {
                 const size_t row = (size_t)b * n + pt;
                 const float4 *f = reinterpret_cast<const float4 *>(a.feat + row * C0);
 #pragma unroll 4
-                for (int c = 0; c < C0 / 8; ++c) {
+                for (int c = cb; c < ce; ++c) {
                     const float4 u0 = __ldg(f + 2 * c), u1 = __ldg(f + 2 * c + 1);
                     st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
                                  Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
                 }
-                const float *p3 = a.xyz + row * 3;
-                store_coord_chunks<T16>(act_row + (C0 / 8) * TC_LBO, act_row + (C0 / 8 + 1) * TC_LBO, __ldg(p3),
-                                        __ldg(p3 + 1), __ldg(p3 + 2));
-                for (int c = C0 / 8 + 2; c < a.Kp[0] / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                if (half == 1) {
+                    const float *p3 = a.xyz + row * 3;
+                    store_coord_chunks<T16>(act_row + cc * TC_LBO, act_row + (cc + 1) * TC_LBO, __ldg(p3),
+                                            __ldg(p3 + 1), __ldg(p3 + 2));
+                    for (int c = cc + 2; c < kc0; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                }
             } else {
-                for (int c = 0; c < a.Kp[0] / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                for (int c = cb; c < ce; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
+                if (half == 1)
+                    for (int c = cc; c < kc0; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
             }
             ptx::fence_proxy_async_smem();
             ptx::mbar_arrive(act_ready);
@@ -478,13 +523,15 @@ head_tc_kernel(HeadArgs a) {
             for (int l = 0; l < HEAD_LAYERS - 1; ++l) {
                 ptx::mbar_wait(layer_done, n_done & 1); ++n_done;
                 ptx::tc_fence_after();
-                epilogue_hidden<T16>(tlane, a.out[l], s_bias + boff, act_row);
+                const int hw = a.out[l] / 2;
+                epilogue_hidden<T16>(tlane, half * hw, half * hw + hw, s_bias + boff, act_row);
                 boff += a.out[l];
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async_smem();
                 ptx::mbar_arrive(act_ready);
             }
-            // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points
+            // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points.
+            //      The halves split the 128 columns; both contribute through atomicMax.
             const int nvalid = min(128, n - p0);
             for (int nc = 0; nc < a.out[HEAD_LAYERS - 1] / 128; ++nc) {
                 const int buf = nc & 1;
@@ -492,26 +539,27 @@ head_tc_kernel(HeadArgs a) {
                 ptx::tc_fence_after();
                 float cur = -INFINITY;
 #pragma unroll
-                for (int c0 = 0; c0 < 128; c0 += 32) {
+                for (int c0 = 0; c0 < 64; c0 += 32) {
                     uint32_t v[32];
-                    ptx::tmem_ld32(tlane + buf * 128 + c0, v);
+                    ptx::tmem_ld32(tlane + buf * 128 + half * 64 + c0, v);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
-                        if (c0 + i < nvalid) cur = fmaxf(cur, __uint_as_float(v[i]));
+                        if (half * 64 + c0 + i < nvalid) cur = fmaxf(cur, __uint_as_float(v[i]));
                 }
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(&fin_free[buf]);
                 const int ch = nc * 128 + r;
                 const float val = fmaxf(cur + s_bias[boff + ch], 0.f);
                 // post-ReLU values are >= 0: their int image is order preserving
-                atomicMax(reinterpret_cast<int *>(a.pooled) + (size_t)b * a.out[HEAD_LAYERS - 1] + ch,
-                          __float_as_int(val));
+                if (half * 64 < nvalid)
+                    atomicMax(reinterpret_cast<int *>(a.pooled) + (size_t)b * a.out[HEAD_LAYERS - 1] + ch,
+                              __float_as_int(val));
             }
         }
     }
     __syncthreads();
-    if (warp == 5) ptx::tmem_dealloc(tmem_base, 512);
+    if (warp == HEAD_MMA_WARP) ptx::tmem_dealloc(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------- host side
