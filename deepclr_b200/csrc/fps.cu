@@ -241,6 +241,14 @@ extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoin
                    B, N, npoint, pt_stride);
     if (B == 0 || npoint == 0) return DCLR_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (N > 2048 && N <= FPS_MAX_RESIDENT_N) {             // exact pruned variant (fps_bucket.cu)
+        void *ws = nullptr;
+        DCLR_CUDA(cudaMallocAsync(&ws, fps_bucket_workspace_bytes(B, N), st));
+        int used = 0;
+        int rc = fps_bucket_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, ws, st, &used);
+        cudaFreeAsync(ws, st);
+        if (rc != DCLR_OK || used) return rc;
+    }
     float *temp = nullptr;
     if (N > FPS_MAX_RESIDENT_N) DCLR_CUDA(cudaMallocAsync(&temp, (size_t)B * N * sizeof(float), st));
     int rc = fps_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, temp, st);

@@ -10,6 +10,11 @@ namespace dclr {
 int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, float *temp_big,
                cudaStream_t st);
 
+// fps_bucket.cu: exact pruned FPS for 2048 < N <= 16384; *used = 0 when the shape is not handled
+size_t fps_bucket_workspace_bytes(int B, int N);
+int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, void *ws,
+                      cudaStream_t st, int *used);
+
 // pointops.cu
 int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
                       const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad,

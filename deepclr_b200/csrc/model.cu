@@ -21,7 +21,7 @@ struct dclr_model {
     int last_launches = 0;
     // carved pointers (valid after ensure_ws)
     int32_t *fps_idx, *bq_idx[2], *bq_cnt[2], *knn_col;
-    void *bq_ws;
+    void *bq_ws, *fps_ws;
     float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
     uint8_t *mask;
     dclr::TcModel *tc = nullptr;     // bf16 tensor-core path (mlp_tc.cu)
@@ -55,6 +55,7 @@ static size_t carve(dclr_model *m, char *base, int G, int N, int B) {
     m->sa_feat = (float *)take((size_t)G * M * m->F * 4);
     m->fps_temp = (float *)take(N > 16384 ? (size_t)G * N * 4 : 0);
     m->bq_ws = take(ball_grid_workspace_bytes(G, N));
+    m->fps_ws = take(fps_bucket_workspace_bytes(G, N));
     const size_t BM = (size_t)B * M;
     const size_t R = BM * (a.knn_k > 0 ? a.knn_k : 1);
     m->knn_col = (int32_t *)take(R * 4);
@@ -130,7 +131,10 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     const dclr_arch &a = m->arch;
     {
         StageScope sc(m, ST_FPS, st);
-        DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+        int used = 0;
+        DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_ws, st, &used));
+        if (used) ++m->last_launches;                      // sort + sample
+        else DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
     }
     {
         StageScope sc(m, ST_BALL, st);
