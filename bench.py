@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument('--kind', default='kitti', choices=['kitti', 'modelnet'])
     ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'fp16'), choices=['fp32', 'fp16', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-latency', action='store_true', help='skip the batch-1 latency loop (ncu launch lists)')
     ap.add_argument('--cpu-pairs', type=int, default=8, help='pairs of the bounded CPU sample')
     return ap.parse_args()
 
@@ -80,6 +81,25 @@ def make_batches(kind, pairs, points, count, seed0):
         s[:, :, :3] += off
         out.append(np.ascontiguousarray(np.concatenate([t, s], 0)))
     return out
+
+
+STAGE_KERNEL = {'fps': 'fps_bucket_kernel', 'ball_query': 'bq_grid_query_kernel', 'knn': 'knn_fast_kernel',
+                'flow_embed': 'flow_tc_kernel', 'pose_head_conv': 'head_tc_kernel', 'sa_mlp_maxpool': 'sa_mlp_kernel'}
+
+
+def ncu_traffic(stage, args):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's main kernel, from the newest committed
+    `ncu --set full` capture of this same workload (profiles/*_ncu_traffic.json, tools/ncu_summary.py); None when the
+    workload differs from the captured one or no capture exists."""
+    import glob
+    if (args.kind, args.pairs, args.points) != ('kitti', 64, 16384):
+        return None
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', '*_ncu_traffic.json')), key=os.path.basename)
+    for f in reversed(files):
+        d = json.load(open(f)).get(STAGE_KERNEL.get(stage, ''))
+        if d:
+            return d['dram_read_bytes'] + d['dram_write_bytes']
+    return None
 
 
 class ClockSampler(threading.Thread):
@@ -219,30 +239,40 @@ def run_native(args, rank, world, local_rank):
     launches = native.last_launches() * args.steps
     value = world * B * args.steps / (ms * 1e-3)
 
-    # ---- end-to-end arm: public API with host buffers, H2D of the inputs and D2H of the poses inside the timed region
-    dbuf = torch.empty_like(resident[0])
-    ybuf = torch.empty((B, 8), dtype=torch.float32).pin_memory()
+    # ---- end-to-end arm: the public host-buffer API (deepclr_b200.models.HostPipeline): every step copies its inputs from
+    # pinned host memory and reads its poses back to the host inside the timed region; the copy of step i+1 is issued on
+    # a copy stream while step i computes (double-buffered device inputs), the host collects the poses of step i-1.
+    from deepclr_b200.models import HostPipeline
+    pipe = HostPipeline(model, depth=2)
+    pipe.run_all(host[i % ROTATE] for i in range(max(3, args.warmup // 2)))
+    pipe.h2d_bytes = pipe.d2h_bytes = 0
+    e2e_out = []
 
-    def step_e2e(i):
-        dbuf.copy_(host[i % ROTATE], non_blocking=True)
-        with torch.no_grad():
-            y = model(dbuf)[0]
-        ybuf[:, :y.shape[1]].copy_(y, non_blocking=True)
+    def run_e2e(steps):
+        e2e_out.append(pipe.run_all(host[i % ROTATE] for i in range(steps)))
 
-    for i in range(max(3, args.warmup // 2)):
-        step_e2e(i)
-    ms_e2e = timed(step_e2e, args.steps)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    run_e2e(args.steps)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item())
+    assert len(e2e_out[0]) == args.steps and all(torch.isfinite(o).all() for o in e2e_out[0])
     e2e = {'value': world * B * args.steps / (ms_e2e * 1e-3), 'unit': 'pairs/s',
-           'h2d_bytes_per_step': host[0].numel() * 4, 'd2h_bytes_per_step': B * 8 * 4,
-           'ms_per_step': ms_e2e / args.steps}
+           'h2d_bytes_per_step': pipe.h2d_bytes // args.steps, 'd2h_bytes_per_step': pipe.d2h_bytes // args.steps,
+           'ms_per_step': ms_e2e / args.steps, 'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches)'}
 
     # ---- batch-1 latency (BASELINE.json configs[1]): p50 of single-pair forwards, CUDA events per call
     lat = []
     one = [r[[0, B]].contiguous() for r in resident]
     with torch.no_grad():
-        for i in range(10):
+        for i in range(0 if args.no_latency else 10):
             model(one[i % ROTATE])
-        for i in range(50):
+        for i in range(1 if args.no_latency else 50):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             model(one[i % ROTATE])
@@ -273,7 +303,7 @@ def run_native(args, rank, world, local_rank):
     else:
         ach = bytes_stage.get(top, 0) / (per_call[top] * 1e-3) / 1e9
         roof = {'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': ach / peaks['hbm']}
-    roof.update({'kernel': top, 'traffic': None, 'peak_source': peaks['src'], 'ms_per_launch': per_call[top],
+    roof.update({'kernel': top, 'traffic': ncu_traffic(top, args), 'peak_source': peaks['src'], 'ms_per_launch': per_call[top],
                  'share_of_step': per_call[top] / (ms / args.steps)})
 
     line = {'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': world, 'steps': args.steps,

@@ -30,3 +30,21 @@ def install_as_deepclr() -> None:
                           ('deepclr.models.base', 'deepclr_b200.models.base'),
                           ('deepclr.models.helper', 'deepclr_b200.models.helper')):
         sys.modules.setdefault(alias, importlib.import_module(target))
+
+
+FPS_TIE_RULES = {'lowest_index': 0, 'reference': 1}
+
+
+def set_fps_tie_rule(rule: str) -> None:
+    """How farthest point sampling resolves bit-equal maxima (include/deepclr_b200.h: dclr_set_fps_tie_rule).
+    'lowest_index' (default, BASELINE.json's stated rule) or 'reference' (the order of the reference's
+    furthest_point_sampling_kernel, sampling_gpu.cu:113-203 -- indices then match that kernel on every input)."""
+    from . import _lib
+    if rule not in FPS_TIE_RULES:
+        raise ValueError(f'rule must be one of {sorted(FPS_TIE_RULES)}')
+    _lib.check(_lib.lib().dclr_set_fps_tie_rule(FPS_TIE_RULES[rule]), 'dclr_set_fps_tie_rule')
+
+
+def get_fps_tie_rule() -> str:
+    from . import _lib
+    return {v: k for k, v in FPS_TIE_RULES.items()}[_lib.lib().dclr_get_fps_tie_rule()]

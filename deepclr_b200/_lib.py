@@ -25,6 +25,8 @@ class DclrArch(ctypes.Structure):
 _SIGNATURES = {
     'dclr_version': (ctypes.c_char_p, []),
     'dclr_last_error': (ctypes.c_char_p, []),
+    'dclr_set_fps_tie_rule': (ctypes.c_int, [ctypes.c_int]),
+    'dclr_get_fps_tie_rule': (ctypes.c_int, []),
     'dclr_fps': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_gather': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_ball_query': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p,

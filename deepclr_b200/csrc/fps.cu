@@ -60,10 +60,24 @@ __device__ __forceinline__ uint64_t lds64(uint32_t addr) {
 // offsets) instead of registers -- needed at T=1024, PP=8 where only 64 registers per thread exist.
 // Per round: packed distance update -> warp redux max -> slot per warp -> barrier -> block max; only the thread(s)
 // holding the block max look up their lowest index and atomicMin it -> barrier.
+// Tie order.  tieL < 0: lowest point index (the stated default).  tieL >= 0: the reference kernel's own order
+// (sampling_gpu.cu:113-203 with a block of 2^tieL threads = opt_n_threads(N), cuda_utils.h:10-14): thread k mod 2^tieL
+// keeps its FIRST strict maximum, and every level of the shared-memory tree keeps the LOWER slot on equal values, so
+// among equal maxima the smallest bit-reversed slot wins, then the smallest k.  rank() is that order as an integer.
+__device__ __forceinline__ int tie_rank(int k, int L) {
+    if (L <= 0) return k;
+    return (int)(((__brev((uint32_t)k & ((1u << L) - 1u)) >> (32 - L)) << (31 - L)) | ((uint32_t)k >> L));
+}
+__device__ __forceinline__ int tie_unrank(int r, int L) {
+    if (L <= 0) return r;
+    const uint32_t slot = __brev((uint32_t)r >> (31 - L)) >> (32 - L), q = (uint32_t)r & ((1u << (31 - L)) - 1u);
+    return (int)((q << L) | slot);
+}
+
 template <int T, int PP, bool ZS>
 __global__ void __launch_bounds__(T, 1)
-fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int32_t *__restrict__ idx_out,
-                    float *__restrict__ new_xyz_out) {
+fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int tieL,
+                    int32_t *__restrict__ idx_out, float *__restrict__ new_xyz_out) {
     extern __shared__ __align__(16) float smem[];
     constexpr int CAP = 2 * T * PP;
     constexpr int NW = T / 32;
@@ -139,15 +153,15 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
         if (bi == m) {
             int cand = INT_MAX;
 #pragma unroll
-            for (int i = PP - 1; i >= 0; --i) {                  // descending: the lowest index survives
+            for (int i = 0; i < PP; ++i) {                       // lowest rank (= lowest index when tieL < 0) survives
                 const int k = 2 * (tid + i * T);
-                cand = __float_as_int(th[i]) == m ? k + 1 : cand;
-                cand = __float_as_int(tl[i]) == m ? k : cand;
+                if (__float_as_int(tl[i]) == m) cand = min(cand, tie_rank(k, tieL));
+                if (__float_as_int(th[i]) == m) cand = min(cand, tie_rank(k + 1, tieL));
             }
             atomicMin(&s_win[par], cand);
         }
         __syncthreads();
-        old = s_win[par];
+        old = tie_unrank(s_win[par], tieL);
         if (tid == 0) idx_out[j] = old;
     }
     if (tid == 0 && new_xyz_out && npoint > 0) {
@@ -161,8 +175,9 @@ fps_resident_kernel(const float *__restrict__ pts, int stride, int N, int npoint
 // tie-break).  temp: [B,N] scratch.
 template <int T>
 __global__ void __launch_bounds__(T, 1)
-fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, float *__restrict__ temp,
+fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, int tieL, float *__restrict__ temp,
                   int32_t *__restrict__ idx_out, float *__restrict__ new_xyz_out) {
+    static_assert(T == 1024, "thread k mod T must own the points the reference's 1024-thread block gives it");
     __shared__ int s_wmax[32];
     __shared__ int s_win[2];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -197,36 +212,39 @@ fps_stream_kernel(const float *__restrict__ pts, int stride, int N, int npoint, 
         int v = lane < (T / 32) ? s_wmax[lane] : INT_MIN;
         const int m = __reduce_max_sync(0xffffffffu, v);
         if (tid == 0) s_win[(j + 1) & 1] = INT_MAX;
-        if (__float_as_int(best) == m) atomicMin(&s_win[j & 1], besti);
+        if (__float_as_int(best) == m) atomicMin(&s_win[j & 1], tie_rank(besti, tieL));
         __syncthreads();
-        old = s_win[j & 1];
+        old = tie_unrank(s_win[j & 1], tieL);
         if (tid == 0) idx_out[j] = old;
     }
 }
 
 template <int T, int PP, bool ZS>
-static int launch_resident(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx,
+static int launch_resident(const float *pts, int stride, int B, int N, int npoint, int tieL, int32_t *idx, float *nx,
                            cudaStream_t st) {
     size_t smem = (size_t)3 * (2 * T * PP) * sizeof(float) + 66 * sizeof(int);
     auto kern = fps_resident_kernel<T, PP, ZS>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<B, T, smem, st>>>(pts, stride, N, npoint, idx, nx);
+    kern<<<B, T, smem, st>>>(pts, stride, N, npoint, tieL, idx, nx);
     DCLR_LAUNCH_CHECK("fps_resident_kernel");
     return DCLR_OK;
 }
 
 int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, float *temp_big,
                cudaStream_t st) {
+    int tieL = -1;
+    if (fps_tie_rule() == 1)
+        for (tieL = 0; (2 << tieL) <= N && tieL < 10; ++tieL) {}          // log2(opt_n_threads(N)), cuda_utils.h:10-14
     // T threads x PP pairs x 2 points >= N
-    if (N <= 256) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 512) return launch_resident<128, 2, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 1024) return launch_resident<128, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 2048) return launch_resident<256, 4, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 4096) return launch_resident<256, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= 8192) return launch_resident<512, 8, false>(pts, stride, B, N, npoint, idx, nx, st);
-    if (N <= FPS_MAX_RESIDENT_N) return launch_resident<1024, 8, true>(pts, stride, B, N, npoint, idx, nx, st);
+    if (N <= 256) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= 512) return launch_resident<128, 2, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= 1024) return launch_resident<128, 4, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= 2048) return launch_resident<256, 4, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= 4096) return launch_resident<256, 8, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= 8192) return launch_resident<512, 8, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
+    if (N <= FPS_MAX_RESIDENT_N) return launch_resident<1024, 8, true>(pts, stride, B, N, npoint, tieL, idx, nx, st);
     if (!temp_big) return fail(DCLR_E_INVALID, "fps: N=%d needs a scratch buffer", N);
-    fps_stream_kernel<1024><<<B, 1024, 0, st>>>(pts, stride, N, npoint, temp_big, idx, nx);
+    fps_stream_kernel<1024><<<B, 1024, 0, st>>>(pts, stride, N, npoint, tieL, temp_big, idx, nx);
     DCLR_LAUNCH_CHECK("fps_stream_kernel");
     return DCLR_OK;
 }

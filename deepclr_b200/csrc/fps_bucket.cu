@@ -12,7 +12,7 @@
 // ORIGINAL index, as everywhere in this library.  In steady state a round touches a handful of the 256 buckets
 // instead of 16384 points; what remains per round is the block-wide argmax (one barrier).
 //
-// Ownership: warp w owns buckets w, w+32, ... (neighbouring buckets land on different warps); lane l owns records
+// Ownership: warp w of NW owns buckets w, w+NW, ... (neighbouring buckets land on different warps); lane l owns records
 // 2l, 2l+1 of each of them (t in registers, coordinates in shared memory); lane i < PP keeps the metadata of the warp's
 // i-th bucket in registers, so the skip test of all of a warp's buckets is one predicated instruction sequence + ballot.
 #include "common.cuh"
@@ -20,6 +20,8 @@
 #include "ptx.cuh"
 #include <float.h>
 #include <limits.h>
+#include <stdlib.h>
+#include <type_traits>
 
 namespace dclr {
 
@@ -165,15 +167,26 @@ __device__ __forceinline__ uint32_t fb_lds32(uint32_t addr) {
     return r;
 }
 
-// PP buckets per warp; capacity CAP = 2048 * PP records.
-template <int PP>
-__global__ void __launch_bounds__(FS_T, 1)
-fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t *__restrict__ idx_out,
+// Tie order of the reference kernel for N > 1024 (1024-thread block, sampling_gpu.cu:113-203): thread tid = k & 1023
+// keeps its first strict maximum, the shared-memory tree keeps the LOWER slot on equal values at every level, so among
+// equal maxima the slot with the smallest bit-reversed tid wins, then the smallest k.  14 bits for N <= 16384.
+__device__ __forceinline__ uint32_t fb_rank16(int k) { return ((__brev((uint32_t)k & 1023u) >> 22) << 4) | ((uint32_t)k >> 10); }
+__device__ __forceinline__ int fb_unrank16(uint32_t r) { return (int)((__brev(r >> 4) >> 22) | ((r & 15u) << 10)); }
+
+// NW warps, PP buckets per warp (bucket g = i * NW + warp); capacity CAP = 64 * NW * PP records.  Fewer, fatter warps
+// win: per round every warp pays the skip test, two warp reductions and the barrier whether or not one of its buckets
+// changes, while only ~9 of the 256 buckets of a 16384-point scan do (issue-bound at 32 warps, ncu r1b).
+template <int NW, int PP>
+__global__ void __launch_bounds__(NW * 32, 1)
+fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_ref, int32_t *__restrict__ idx_out,
                   float *__restrict__ new_xyz_out) {
     extern __shared__ __align__(16) float smem[];
-    constexpr int CAP = 2048 * PP;
+    constexpr int CAP = 64 * NW * PP;
+    constexpr int T = NW * 32;
+    constexpr int WSTRIDE = 64 * NW;           // records between a warp's consecutive buckets
+    static_assert(PP <= 32 && NW <= 32, "lane i keeps bucket i; lane w reads warp w's slot");
     float *s_x = smem, *s_y = smem + CAP, *s_z = smem + 2 * CAP;
-    uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem + 3 * CAP);             // original index per record
+    uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem + 3 * CAP);             // tie rank of the original index
     int2 *s_slot = reinterpret_cast<int2 *>(s_idx + CAP);                       // [2][32] (max bits, key)
     int *s_start = reinterpret_cast<int *>(s_slot + 64);
 
@@ -182,12 +195,12 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t 
     idx_out += (size_t)b * npoint;
     if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
 
-    for (int k = tid; k < CAP; k += FS_T) {
+    for (int k = tid; k < CAP; k += T) {
         if (k < N) {
             const float4 r = __ldg(sorted + k);
             const int oi = __float_as_int(r.w);
             s_x[k] = r.x; s_y[k] = r.y; s_z[k] = r.z;
-            s_idx[k] = (uint16_t)oi;
+            s_idx[k] = (uint16_t)(tie_ref ? fb_rank16(oi) : oi);            // tie order (fb_rank16 above)
             if (oi == 0) *s_start = k;
         } else {
             s_x[k] = 0.f; s_y[k] = 0.f; s_z[k] = 0.f; s_idx[k] = 0xffffu;
@@ -199,12 +212,12 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t 
     float tl[PP], th[PP];
     float blx = 0.f, bly = 0.f, blz = 0.f, bhx = 0.f, bhy = 0.f, bhz = 0.f, bm = -1.0f;
     uint32_t bkey = 0xffffffffu;
-    const uint32_t rec0 = (uint32_t)(64 * warp + 2 * lane);                    // record of pair 0; pair i: + 2048 * i
+    const uint32_t rec0 = (uint32_t)(64 * warp + 2 * lane);                    // record of pair 0; pair i: + WSTRIDE * i
     const uint32_t ax = ptx::smem_u32(s_x) + rec0 * 4, ay = ptx::smem_u32(s_y) + rec0 * 4,
                    az = ptx::smem_u32(s_z) + rec0 * 4, ai = ptx::smem_u32(s_idx) + rec0 * 2;
 #pragma unroll
     for (int i = 0; i < PP; ++i) {
-        const int p = (int)rec0 + 2048 * i;
+        const int p = (int)rec0 + WSTRIDE * i;
         const bool v0 = p < N, v1 = p + 1 < N;
         tl[i] = v0 ? 1e10f : -1.0f;            // -1 can never win (reference: best starts at -1, strict >)
         th[i] = v1 ? 1e10f : -1.0f;
@@ -245,24 +258,35 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t 
         const unsigned mask = __ballot_sync(0xffffffffu, need);
         if (mask) {
             const uint64_t xo = fb_pack2(x1, x1), yo = fb_pack2(y1, y1), zo = fb_pack2(z1, z1);
-#pragma unroll
-            for (int i = 0; i < PP; ++i) {
-                if ((mask >> i) & 1u) {                          // warp-uniform
-                    const uint64_t dx = fb_sub2(fb_lds64(ax + i * 8192), xo), dy = fb_sub2(fb_lds64(ay + i * 8192), yo),
-                                   dz = fb_sub2(fb_lds64(az + i * 8192), zo);
-                    const uint32_t id2 = fb_lds32(ai + i * 4096);
+            // one bucket's update; i is a compile-time constant so tl/th stay in registers
+            auto upd = [&](const int i) {
+                {
+                    const uint64_t dx = fb_sub2(fb_lds64(ax + i * (WSTRIDE * 4)), xo),
+                                   dy = fb_sub2(fb_lds64(ay + i * (WSTRIDE * 4)), yo),
+                                   dz = fb_sub2(fb_lds64(az + i * (WSTRIDE * 4)), zo);
+                    const uint32_t id2 = fb_lds32(ai + i * (WSTRIDE * 2));
                     const uint64_t d2 = fb_fma2(dz, dz, fb_fma2(dx, dx, fb_mul2(dy, dy)));
                     float dl, dh;
                     fb_unpack2(d2, dl, dh);
                     tl[i] = fminf(dl, tl[i]);
                     th[i] = fminf(dh, th[i]);
                     const int bmx = __reduce_max_sync(0xffffffffu, __float_as_int(fmaxf(tl[i], th[i])));
-                    const uint32_t p = rec0 + 2048u * i;
+                    const uint32_t p = rec0 + (uint32_t)WSTRIDE * i;
                     const uint32_t klo = __float_as_int(tl[i]) == bmx ? ((id2 & 0xffffu) << 16 | p) : 0xffffffffu;
                     const uint32_t khi = __float_as_int(th[i]) == bmx ? ((id2 >> 16) << 16 | (p + 1)) : 0xffffffffu;
                     const uint32_t kmin = __reduce_min_sync(0xffffffffu, min(klo, khi));
                     if (lane == i) { bm = __int_as_float(bmx); bkey = kmin; }
                 }
+            };
+            // warp-uniform scan of the mask, a clean byte at a time.  (A jump table -- switch on ffs(mask) -- was
+            // measured SLOWER: 0.71 vs 0.53 ms per 128 clouds; the indirect branch costs more than the untaken tests.)
+            constexpr int GR = PP < 8 ? PP : 8;
+#pragma unroll
+            for (int q = 0; q < PP / GR; ++q) {
+                if (PP > 8 && ((mask >> (q * GR)) & 0xffu) == 0) continue;
+#pragma unroll
+                for (int r = 0; r < GR; ++r)
+                    if ((mask >> (q * GR + r)) & 1u) upd(q * GR + r);
             }
         }
         // ---- warp best over its buckets, block best over the warps (one barrier; slots double-buffered by parity)
@@ -272,11 +296,11 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t 
         int2 *slot = s_slot + (j & 1) * 32;
         if (lane == 0) slot[warp] = make_int2(wm, (int)wk);
         __syncthreads();
-        const int2 e = slot[lane];
+        const int2 e = lane < NW ? slot[lane] : make_int2(INT_MIN, -1);
         const int m = __reduce_max_sync(0xffffffffu, e.x);
         const uint32_t key = __reduce_min_sync(0xffffffffu, e.x == m ? (uint32_t)e.y : 0xffffffffu);
         oldpos = (int)(key & 0xffffu);
-        if (tid == 0) idx_out[j] = (int)(key >> 16);
+        if (tid == 0) idx_out[j] = tie_ref ? fb_unrank16(key >> 16) : (int)(key >> 16);
     }
     if (tid == 0 && new_xyz_out && npoint > 0) {
         new_xyz_out[(npoint - 1) * 3 + 0] = s_x[oldpos];
@@ -287,12 +311,13 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int32_t 
 
 size_t fps_bucket_workspace_bytes(int B, int N) { return (size_t)B * N * sizeof(float4) + 256; }
 
-template <int PP>
-static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int32_t *idx, float *nx, cudaStream_t st) {
-    const size_t smem = (size_t)2048 * PP * 14 + 64 * sizeof(int2) + 16;
-    auto kern = fps_bucket_kernel<PP>;
+template <int NW, int PP>
+static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
+                         cudaStream_t st) {
+    const size_t smem = (size_t)64 * NW * PP * 14 + 64 * sizeof(int2) + 16;
+    auto kern = fps_bucket_kernel<NW, PP>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<B, FS_T, smem, st>>>(sorted, N, npoint, idx, nx);
+    kern<<<B, NW * 32, smem, st>>>(sorted, N, npoint, tie_ref, idx, nx);
     DCLR_LAUNCH_CHECK("fps_bucket_kernel");
     return DCLR_OK;
 }
@@ -301,14 +326,18 @@ static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int32_t
 int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, void *ws,
                       cudaStream_t st, int *used) {
     *used = 0;
+    const int tie_ref = fps_tie_rule() == 1;
     if (N <= 2048 || N > 16384 || npoint < 2) return DCLR_OK;
     float4 *sorted = (float4 *)ws;
     fps_sort_kernel<<<B, FS_T, 0, st>>>(pts, stride, N, sorted);
     DCLR_LAUNCH_CHECK("fps_sort_kernel");
     int rc;
-    if (N <= 4096) rc = launch_bucket<2>(sorted, B, N, npoint, idx, nx, st);
-    else if (N <= 8192) rc = launch_bucket<4>(sorted, B, N, npoint, idx, nx, st);
-    else rc = launch_bucket<8>(sorted, B, N, npoint, idx, nx, st);
+    static const int shape = getenv("DCLR_FPS_SHAPE") ? atoi(getenv("DCLR_FPS_SHAPE")) : 0;   // tuning knob (tools/)
+    if (N <= 4096) rc = launch_bucket<32, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else if (N <= 8192) rc = launch_bucket<32, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else if (shape == 32) rc = launch_bucket<32, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else if (shape == 16) rc = launch_bucket<16, 16>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else rc = launch_bucket<8, 32>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     if (rc == DCLR_OK) *used = 1;
     return rc;
 }

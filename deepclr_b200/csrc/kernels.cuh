@@ -7,6 +7,7 @@
 namespace dclr {
 
 // fps.cu
+int fps_tie_rule();        // 0 = lowest index, 1 = the reference kernel's tree order (core.cu)
 int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, float *temp_big,
                cudaStream_t st);
 

@@ -370,6 +370,13 @@ flow_tc_kernel(FlowArgs a) {
 }
 
 // ---------------------------------------------------------------- output head
+#ifdef DCLR_TRACE
+// tools/head_trace.py: SM-clock timestamps of CTA 0's roles (build -DDCLR_TRACE only)
+__device__ long long g_trace[1024];
+#define TRACE(slot) do { if (blockIdx.x == 0 && (slot) < 1024) g_trace[(slot)] = clock64(); } while (0)
+#else
+#define TRACE(slot) do { } while (0)
+#endif
 constexpr int HEAD_LAYERS = 5;
 constexpr int HEAD_KT = 64;                      // K elements per streamed weight tile (128 rows x 64 = 16 KB)
 constexpr int HEAD_STAGES = 5;
@@ -447,6 +454,7 @@ head_tc_kernel(HeadArgs a) {
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
                     ptx::tc_fence_after();
+                    TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
                     const bool last = l == HEAD_LAYERS - 1;
                     for (int nc = 0; nc < a.out[l] / 128; ++nc) {
                         uint32_t dcol = tmem_base + nc * 128;
@@ -476,6 +484,7 @@ head_tc_kernel(HeadArgs a) {
                         if (last) ptx::mma_commit(&fin_done[nc & 1]);
                     }
                     if (!last) ptx::mma_commit(layer_done);
+                    TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
                 }
             }
         }
@@ -493,6 +502,8 @@ head_tc_kernel(HeadArgs a) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * 128;
             const int pt = p0 + r;
+            const int tr0 = ((tile - blockIdx.x) / gridDim.x) * 64 + 16;
+            if (tid == 0) TRACE(tr0);
             // ---- input rows: [motion feat (C0) | xyz hi,hi,lo | 0]; half 0 writes the first feature chunks, half 1
             //      the rest, the coordinates and the padding
             const int cb = half == 0 ? 0 : cmid, ce = half == 0 ? cmid : cc;
@@ -517,17 +528,20 @@ head_tc_kernel(HeadArgs a) {
                     for (int c = cc; c < kc0; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
             }
             ptx::fence_proxy_async_smem();
+            if (tid == 0) TRACE(tr0 + 1);
             ptx::mbar_arrive(act_ready);
             // ---- hidden layers: accumulators -> activations, in place
             int boff = 0;
             for (int l = 0; l < HEAD_LAYERS - 1; ++l) {
                 ptx::mbar_wait(layer_done, n_done & 1); ++n_done;
                 ptx::tc_fence_after();
+                if (tid == 0) TRACE(tr0 + 2 + l * 2);
                 const int hw = a.out[l] / 2;
                 epilogue_hidden<T16>(tlane, half * hw, half * hw + hw, s_bias + boff, act_row);
                 boff += a.out[l];
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async_smem();
+                if (tid == 0) TRACE(tr0 + 3 + l * 2);
                 ptx::mbar_arrive(act_ready);
             }
             // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points.
@@ -537,6 +551,7 @@ head_tc_kernel(HeadArgs a) {
                 const int buf = nc & 1;
                 ptx::mbar_wait(&fin_done[buf], fin_cnt[buf] & 1); ++fin_cnt[buf];
                 ptx::tc_fence_after();
+                if (tid == 0) TRACE(tr0 + 10 + nc);
                 float cur = -INFINITY;
 #pragma unroll
                 for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -590,6 +605,12 @@ static int pack_any(int fmt, const float *W, int out, int in, int nfeat, int row
     return fmt == 1 ? pack_rows<__nv_bfloat16>(W, out, in, nfeat, row0, R, k0, Kt, dst)
                     : pack_rows<__half>(W, out, in, nfeat, row0, R, k0, Kt, dst);
 }
+
+#ifdef DCLR_TRACE
+extern "C" int dclr_debug_read_trace(long long *dst, int n) {
+    return cudaMemcpyFromSymbol(dst, g_trace, sizeof(long long) * (n < 1024 ? n : 1024)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 void tc_destroy(TcModel *t) {
     if (!t) return;

@@ -1,5 +1,6 @@
 from .base import BaseModel, ModelInferenceHelper
+from .stream import HostPipeline
 from .build import build_model, load_trained_model, ModelType, store_models_code
 
-__all__ = ['BaseModel', 'ModelInferenceHelper',
+__all__ = ['BaseModel', 'ModelInferenceHelper', 'HostPipeline',
            'build_model', 'load_trained_model', 'ModelType', 'store_models_code']

@@ -154,3 +154,21 @@ def test_batch_independence_full_size():
         parts = [model(torch.from_numpy(sharding.shard_batch(x, 4, r)).to(DEV))[0] for r in range(4)]
     np.testing.assert_array_equal(torch.cat(parts).cpu().numpy(), y_all.cpu().numpy())
     assert torch.isfinite(y_all).all()
+
+
+def test_host_pipeline_equals_direct_forward():
+    """HostPipeline (double-buffered H2D on a copy stream, poses into pinned buffers) returns, batch by batch, exactly
+    what a direct forward of the same batch returns -- 7 batches through 2 device slots, ragged last batch."""
+    from deepclr_b200 import synth
+    from deepclr_b200.models import HostPipeline
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    hosts = [torch.from_numpy(synth.batch('kitti', 3 if i < 6 else 1, 300 + 10 * i, n=2048)).pin_memory()
+             for i in range(7)]
+    pipe = HostPipeline(model, depth=2)
+    got = pipe.run_all(hosts)
+    assert len(got) == 7 and pipe.h2d_bytes == sum(h.numel() * 4 for h in hosts)
+    for h, y in zip(hosts, got):
+        with torch.no_grad():
+            want = model(h.to(DEV))[0].cpu()
+        np.testing.assert_array_equal(y.numpy(), want.numpy())

@@ -60,6 +60,25 @@ def test_fps_exact_ties_take_lowest_index(p2):
     assert np.array_equal(p2.furthest_point_sample(_t(xyz), 100).cpu().numpy(), want)
 
 
+@pytest.mark.parametrize('N,npoint', [(1, 1), (7, 7), (100, 60), (700, 300), (1024, 400), (1500, 500), (2048, 64),
+                                      (3000, 500), (6000, 300), (16384, 256), (17000, 64)])
+def test_fps_reference_tie_rule_matches_faithful_oracle(p2, N, npoint):
+    """dclr_set_fps_tie_rule(1): the block-tree order of sampling_gpu.cu:113-203 (restated in oracle_fps, block size
+    opt_n_threads(N) incl. the non-power-of-two N < 1024 cases) on integer lattices where most rounds tie."""
+    import deepclr_b200
+    rng = np.random.default_rng(N)
+    xyz = rng.integers(0, 10, (2, N, 3)).astype(np.float32)
+    _, ties = ops.fps_lowidx(xyz, npoint, return_ties=True)
+    assert N < 100 or ties.sum() > 0
+    deepclr_b200.set_fps_tie_rule('reference')
+    try:
+        assert deepclr_b200.get_fps_tie_rule() == 'reference'
+        got = p2.furthest_point_sample(_t(xyz), npoint).cpu().numpy()
+    finally:
+        deepclr_b200.set_fps_tie_rule('lowest_index')
+    assert np.array_equal(got, ops.fps(xyz, npoint))
+
+
 def test_fps_point_stride_4_and_new_xyz():
     from deepclr_b200 import _lib
     rng = np.random.default_rng(5)

@@ -27,9 +27,40 @@ def test_fps_equals_reference_kernel(p2, kind, B, N, npoint):
     x = torch.from_numpy(xyz).to(DEV)
     want = ref_cuda.furthest_point_sample(x, npoint).cpu().numpy()
     got = p2.furthest_point_sample(x, npoint).cpu().numpy()
-    # identical unless a round had an exact tie of the running maximum (tie rules differ by design: lowest index here,
-    # tree position in sampling_gpu.cu:86-91); generic float data has none
+    # identical unless a round had an exact tie of the running maximum (the default rule is the lowest index, the
+    # reference's is the tree position of sampling_gpu.cu:86-91); these seeds have none
     assert np.array_equal(got, want)
+
+
+@pytest.fixture
+def reference_tie_rule():
+    import deepclr_b200
+    deepclr_b200.set_fps_tie_rule('reference')
+    yield
+    deepclr_b200.set_fps_tie_rule('lowest_index')
+
+
+@pytest.mark.parametrize('kind,B,N,npoint', [('lattice', 2, 700, 300), ('lattice', 2, 3000, 600), ('dup', 3, 1024, 512),
+                                             ('dup', 2, 5000, 700), ('dup', 2, 16384, 1024), ('dup', 1, 20000, 300),
+                                             ('kitti', 16, 16384, 1024), ('kitti', 2, 40000, 2500)])
+def test_fps_reference_tie_rule_is_bit_identical_to_reference_kernel(p2, reference_tie_rule, kind, B, N, npoint):
+    """With dclr_set_fps_tie_rule(1) the sampled indices equal the reference kernel's on EVERY input, exact ties
+    included: integer lattices and duplicated points (many bit-equal maxima), and 16 full-size KITTI-shaped scans
+    (where ~1 round in 10^4 ties by chance).  All three kernels: resident (N <= 2048), bucketed, streaming."""
+    from deepclr_b200 import synth
+    rng = np.random.default_rng(N + npoint)
+    if kind == 'lattice':
+        xyz = rng.integers(0, 12, (B, N, 3)).astype(np.float32)
+    elif kind == 'dup':
+        xyz = rng.uniform(-40, 40, (B, N, 3)).astype(np.float32)
+        src = rng.integers(0, N, N // 3)
+        xyz[:, rng.permutation(N)[:N // 3]] = xyz[:, src]          # a third of the points are exact copies
+    else:
+        xyz = synth.batch('kitti', B // 2, 100, n=N)[:, :, :3].copy()
+    x = torch.from_numpy(np.ascontiguousarray(xyz)).to(DEV)
+    want = ref_cuda.furthest_point_sample(x, npoint)
+    got = p2.furthest_point_sample(x, npoint)
+    assert torch.equal(got, want), f'first mismatch at {torch.nonzero(got != want)[:3].tolist()}'
 
 
 @pytest.mark.parametrize('N,M,r,ns', [(16384, 1024, 0.5, 512), (16384, 1024, 1.0, 1024), (1024, 512, 0.2, 512),

@@ -1,0 +1,111 @@
+"""Op-level sweep (BASELINE.json configs[4]): FPS / ball query / kNN at 1k-128k points, this library's kernels through
+the C ABI vs the reference's own CUDA kernels (oracle/_ref, sm_100a rebuild) on the same inputs, with bit-exact index
+comparison.  One JSON line per (op, N).  GPU only; run on the B200 box:
+
+    python tools/op_sweep.py [--sizes 1024,2048,...] [--clouds 8] > gpurun_out/op_sweep.jsonl
+
+Bytes are the algorithmic (compulsory) bytes of SURVEY.md 8(d): FPS B(12N+4M), ball query B(12N+12M+4M*ns),
+kNN 12(Nx+Ny)+16*Ny*k per batch element.  Timing: CUDA events on the current stream, median of `--iters` after warm-up.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def timed(fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--sizes', default='1024,2048,4096,8192,16384,32768,65536,131072')
+    ap.add_argument('--clouds', type=int, default=8)
+    ap.add_argument('--iters', type=int, default=10)
+    ap.add_argument('--ops', default='fps,ball,knn')
+    ap.add_argument('--no-ref', action='store_true')
+    args = ap.parse_args()
+    from deepclr_b200 import synth
+    from deepclr_b200.pointnet2 import pointnet2_utils as pu
+    from deepclr_b200.torch_cluster import knn
+    from oracle import ref_cuda
+    have_ref = ref_cuda.available() and not args.no_ref
+    peak = 6453.7
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        peak = float(json.load(open(p))['hbm_gbs'])
+    dev = torch.device('cuda:0')
+    B = args.clouds
+    ops = args.ops.split(',')
+    for N in [int(s) for s in args.sizes.split(',')]:
+        clouds = np.stack([synth.kitti_pair(100 + i, N)[0][:, :3] for i in range(B)]).astype(np.float32)
+        xyz = torch.from_numpy(np.ascontiguousarray(clouds)).to(dev)
+        M = max(N // 16, 1)
+        if 'fps' in ops:
+            ms = timed(lambda: pu.furthest_point_sample(xyz, M), args.iters)
+            idx = pu.furthest_point_sample(xyz, M)
+            line = {'op': 'fps', 'N': N, 'npoint': M, 'clouds': B, 'ms': ms,
+                    'alg_GBps': B * (12 * N + 4 * M) / ms / 1e6, 'hbm_peak_GBps': peak,
+                    'streamed_equiv_GBps': B * (M - 1) * N * 16 / ms / 1e6}
+            if have_ref:
+                rms = timed(lambda: ref_cuda.furthest_point_sample(xyz, M), max(3, args.iters // 3), warm=1)
+                ridx = ref_cuda.furthest_point_sample(xyz, M)
+                line.update(ref_ms=rms, speedup=rms / ms, bit_exact=bool(torch.equal(idx, ridx)))
+            print(json.dumps(line), flush=True)
+        else:
+            idx = pu.furthest_point_sample(xyz, M)
+        new_xyz = torch.gather(xyz, 1, idx.long().unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+        if 'ball' in ops:
+            for r, ns in ((0.5, 512), (1.0, 1024)):
+                ms = timed(lambda: pu.ball_query(r, ns, xyz, new_xyz), args.iters)
+                bi = pu.ball_query(r, ns, xyz, new_xyz)
+                nbytes = B * (12 * N + 12 * M + 4 * M * ns)
+                line = {'op': 'ball_query', 'N': N, 'M': M, 'radius': r, 'nsample': ns, 'clouds': B, 'ms': ms,
+                        'alg_GBps': nbytes / ms / 1e6, 'hbm_peak_GBps': peak, 'frac_of_hbm': nbytes / ms / 1e6 / peak}
+                if have_ref:
+                    rms = timed(lambda: ref_cuda.ball_query(r, ns, xyz, new_xyz), max(3, args.iters // 3), warm=1)
+                    rbi = ref_cuda.ball_query(r, ns, xyz, new_xyz)
+                    line.update(ref_ms=rms, speedup=rms / ms, bit_exact=bool(torch.equal(bi, rbi)))
+                print(json.dumps(line), flush=True)
+        if 'knn' in ops and N <= 16384:
+            for k in (20, 30):
+                if k > N:
+                    continue
+                # query = cloud b, candidates = a second, independently sampled cloud of the same size
+                src = np.stack([synth.kitti_pair(100 + i, N)[1][:, :3] for i in range(B)]).astype(np.float32)
+                xs = torch.from_numpy(np.ascontiguousarray(src)).to(dev).view(B * N, 3)
+                ys = xyz.view(B * N, 3)
+                bt = torch.arange(B, device=dev).repeat_interleave(N)
+                ms = timed(lambda: knn(xs, ys, k, bt, bt), args.iters)
+                out = knn(xs, ys, k, bt, bt)
+                nbytes = B * (12 * 2 * N + 16 * N * k)
+                line = {'op': 'knn', 'Nx': N, 'Ny': N, 'k': k, 'batch': B, 'ms': ms, 'alg_GBps': nbytes / ms / 1e6,
+                        'hbm_peak_GBps': peak}
+                if N <= 8192 and not args.no_ref:
+                    rms = timed(lambda: ref_cuda.knn_standin(xs, ys, k, B), 3, warm=1)
+                    ref = ref_cuda.knn_standin(xs, ys, k, B)
+                    same = float((out[1] == ref[1]).float().mean().item())
+                    line.update(standin_ms=rms, speedup_vs_standin=rms / ms, index_agreement_with_standin=same,
+                                note='stand-in = torch.cdist^2 + topk (torch_cluster absent); cdist rounds differently')
+                print(json.dumps(line), flush=True)
+
+
+if __name__ == '__main__':
+    main()
