@@ -173,6 +173,18 @@ __device__ __forceinline__ uint32_t fb_lds32(uint32_t addr) {
 __device__ __forceinline__ uint32_t fb_rank16(int k) { return ((__brev((uint32_t)k & 1023u) >> 22) << 4) | ((uint32_t)k >> 10); }
 __device__ __forceinline__ int fb_unrank16(uint32_t r) { return (int)((__brev(r >> 4) >> 22) | ((r & 15u) << 10)); }
 
+#ifdef DCLR_TRACE
+__device__ long long g_fps_trace[4096];
+#define FTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && j >= 500 && j < 532) g_fps_trace[((j - 500) * 8 + warp) * 16 + (slot)] = clock64(); } while (0)
+#define FTRACEV(slot, v) do { if (blockIdx.x == 0 && lane == 0 && j >= 500 && j < 532) g_fps_trace[((j - 500) * 8 + warp) * 16 + (slot)] = (v); } while (0)
+extern "C" int dclr_debug_read_fps_trace(long long *dst, int n) {
+    return cudaMemcpyFromSymbol(dst, g_fps_trace, sizeof(long long) * (n < 4096 ? n : 4096)) == cudaSuccess ? 0 : -1;
+}
+#else
+#define FTRACE(slot) do { } while (0)
+#define FTRACEV(slot, v) do { } while (0)
+#endif
+
 // NW warps, PP buckets per warp (bucket g = i * NW + warp); capacity CAP = 64 * NW * PP records.  Fewer, fatter warps
 // win: per round every warp pays the skip test, two warp reductions and the barrier whether or not one of its buckets
 // changes, while only ~9 of the 256 buckets of a 16384-point scan do (issue-bound at 32 warps, ncu r1b).
@@ -247,6 +259,7 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_
         if (tid == 0 && new_xyz_out) {
             new_xyz_out[(j - 1) * 3 + 0] = x1; new_xyz_out[(j - 1) * 3 + 1] = y1; new_xyz_out[(j - 1) * 3 + 2] = z1;
         }
+        FTRACE(0);
         // ---- which of this warp's buckets can change?  (lane i tests bucket i)
         bool need = false;
         if (lane < PP) {
@@ -255,31 +268,32 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_
             const float lb = (ex * ex + ey * ey + ez * ez) * 0.9999f;
             need = lb < bm;
         }
+        // (vote.ballot beats redux.or here -- 0.534 vs 0.578 ms -- although only the latter yields a uniform register)
         const unsigned mask = __ballot_sync(0xffffffffu, need);
+        FTRACE(1);
+        FTRACEV(6, __popc(mask));
         if (mask) {
             const uint64_t xo = fb_pack2(x1, x1), yo = fb_pack2(y1, y1), zo = fb_pack2(z1, z1);
-            // one bucket's update; i is a compile-time constant so tl/th stay in registers
+            // warp-uniform scan of the mask, a clean byte at a time; i is a compile-time constant so tl/th stay in
+            // registers.  (Measured alternatives, tools/fps_trace.py + tools/micro/lat2.cu: a jump table on ffs(mask)
+            // costs ~120 cycles per indirect branch and was slower, 0.71 vs 0.53 ms per 128 clouds.)
             auto upd = [&](const int i) {
-                {
-                    const uint64_t dx = fb_sub2(fb_lds64(ax + i * (WSTRIDE * 4)), xo),
-                                   dy = fb_sub2(fb_lds64(ay + i * (WSTRIDE * 4)), yo),
-                                   dz = fb_sub2(fb_lds64(az + i * (WSTRIDE * 4)), zo);
-                    const uint32_t id2 = fb_lds32(ai + i * (WSTRIDE * 2));
-                    const uint64_t d2 = fb_fma2(dz, dz, fb_fma2(dx, dx, fb_mul2(dy, dy)));
-                    float dl, dh;
-                    fb_unpack2(d2, dl, dh);
-                    tl[i] = fminf(dl, tl[i]);
-                    th[i] = fminf(dh, th[i]);
-                    const int bmx = __reduce_max_sync(0xffffffffu, __float_as_int(fmaxf(tl[i], th[i])));
-                    const uint32_t p = rec0 + (uint32_t)WSTRIDE * i;
-                    const uint32_t klo = __float_as_int(tl[i]) == bmx ? ((id2 & 0xffffu) << 16 | p) : 0xffffffffu;
-                    const uint32_t khi = __float_as_int(th[i]) == bmx ? ((id2 >> 16) << 16 | (p + 1)) : 0xffffffffu;
-                    const uint32_t kmin = __reduce_min_sync(0xffffffffu, min(klo, khi));
-                    if (lane == i) { bm = __int_as_float(bmx); bkey = kmin; }
-                }
+                const uint64_t dx = fb_sub2(fb_lds64(ax + i * (WSTRIDE * 4)), xo),
+                               dy = fb_sub2(fb_lds64(ay + i * (WSTRIDE * 4)), yo),
+                               dz = fb_sub2(fb_lds64(az + i * (WSTRIDE * 4)), zo);
+                const uint32_t id2 = fb_lds32(ai + i * (WSTRIDE * 2));
+                const uint64_t d2 = fb_fma2(dz, dz, fb_fma2(dx, dx, fb_mul2(dy, dy)));
+                float dl, dh;
+                fb_unpack2(d2, dl, dh);
+                tl[i] = fminf(dl, tl[i]);
+                th[i] = fminf(dh, th[i]);
+                const int bmx = __reduce_max_sync(0xffffffffu, __float_as_int(fmaxf(tl[i], th[i])));
+                const uint32_t p = rec0 + (uint32_t)WSTRIDE * i;
+                const uint32_t klo = __float_as_int(tl[i]) == bmx ? ((id2 & 0xffffu) << 16 | p) : 0xffffffffu;
+                const uint32_t khi = __float_as_int(th[i]) == bmx ? ((id2 >> 16) << 16 | (p + 1)) : 0xffffffffu;
+                const uint32_t kmin = __reduce_min_sync(0xffffffffu, min(klo, khi));
+                if (lane == i) { bm = __int_as_float(bmx); bkey = kmin; }
             };
-            // warp-uniform scan of the mask, a clean byte at a time.  (A jump table -- switch on ffs(mask) -- was
-            // measured SLOWER: 0.71 vs 0.53 ms per 128 clouds; the indirect branch costs more than the untaken tests.)
             constexpr int GR = PP < 8 ? PP : 8;
 #pragma unroll
             for (int q = 0; q < PP / GR; ++q) {
@@ -289,17 +303,20 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_
                     if ((mask >> (q * GR + r)) & 1u) upd(q * GR + r);
             }
         }
+        FTRACE(2);
         // ---- warp best over its buckets, block best over the warps (one barrier; slots double-buffered by parity)
         const int mybits = lane < PP ? __float_as_int(bm) : INT_MIN;
         const int wm = __reduce_max_sync(0xffffffffu, mybits);
         const uint32_t wk = __reduce_min_sync(0xffffffffu, (lane < PP && mybits == wm) ? bkey : 0xffffffffu);
         int2 *slot = s_slot + (j & 1) * 32;
         if (lane == 0) slot[warp] = make_int2(wm, (int)wk);
+        FTRACE(3);
         __syncthreads();
         const int2 e = lane < NW ? slot[lane] : make_int2(INT_MIN, -1);
         const int m = __reduce_max_sync(0xffffffffu, e.x);
         const uint32_t key = __reduce_min_sync(0xffffffffu, e.x == m ? (uint32_t)e.y : 0xffffffffu);
         oldpos = (int)(key & 0xffffu);
+        FTRACEV(4, clock64() + (oldpos & 0));
         if (tid == 0) idx_out[j] = tie_ref ? fb_unrank16(key >> 16) : (int)(key >> 16);
     }
     if (tid == 0 && new_xyz_out && npoint > 0) {

@@ -39,6 +39,8 @@ struct SaArgs {
     const float *w_host[2];  // HOST copies, per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
                              // (they travel in the kernel parameter block = constant bank)
     float *out;              // [B,M,ld_out] point-major; scale s writes columns [s*H3, (s+1)*H3)
+    uint16_t *out16 = nullptr;   // optional 16-bit copy (fmt16: 1 bf16, 2 fp16) read by the tensor-core flow kernel
+    int fmt16 = 0;
     int N, M, ld_out, nscales;
 };
 int sa_mlp_launch(const SaArgs &a, int B, int cin, const int *h, cudaStream_t st);

@@ -54,6 +54,11 @@ template <> struct Cvt<__nv_bfloat16> {
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
     }
+    static __device__ __forceinline__ uint32_t pack_relu(uint32_t a, uint32_t b) {     // max(.,0) then round
+        uint32_t r;
+        asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(b)), "f"(__uint_as_float(a)));
+        return r;
+    }
     static __device__ __forceinline__ uint16_t one(float a) {
         __nv_bfloat16 v = __float2bfloat16_rn(a);
         return *reinterpret_cast<uint16_t *>(&v);
@@ -68,6 +73,11 @@ template <> struct Cvt<__half> {
         b = fminf(fmaxf(b, -65504.f), 65504.f);
         __half2 v = __floats2half2_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
+    }
+    static __device__ __forceinline__ uint32_t pack_relu(uint32_t a, uint32_t b) {     // max(.,0), round, saturate
+        uint32_t r;
+        asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(b)), "f"(__uint_as_float(a)));
+        return r;
     }
     static __device__ __forceinline__ uint16_t one(float a) {
         a = fminf(fmaxf(a, -65504.f), 65504.f);
@@ -89,15 +99,22 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 // (hi = value rounded to 16 bits, lo = rounded remainder), i.e. the coordinate contribution w*c is evaluated as
 // w_hi*c_hi + w_lo*c_hi + w_hi*c_lo with ~16 significant bits: metre-scale coordinates (up to 80 m on LiDAR scans)
 // would otherwise lose centimetres to the 8-bit bf16 mantissa.  The columns live in what is padding anyway.
+// bias (nullable) folds the layer bias into the GEMM: columns kbias / kbias + 1 hold b_hi / b_lo and meet two columns
+// of ONES in the activations, so the accumulator already contains x.W + b (to ~16 significant bits of b) and the
+// hidden-layer epilogue is a single cvt.rn.relu per value pair.
 template <typename T16>
-__global__ void pack_tile_kernel(const float *__restrict__ W, int out, int in, int nfeat, int row0, int R, int k0,
-                                 int Kt, uint16_t *__restrict__ dst) {
+__global__ void pack_tile_kernel(const float *__restrict__ W, const float *__restrict__ bias, int kbias, int out, int in,
+                                 int nfeat, int row0, int R, int k0, int Kt, uint16_t *__restrict__ dst) {
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= R * Kt) return;
     int kk = e % Kt, r = e / Kt;
     int kp = k0 + kk, row = row0 + r;
     uint16_t q = 0;
-    if (row < out) {
+    if (row < out && bias != nullptr && (kp == kbias || kp == kbias + 1)) {
+        const float bv = bias[row];
+        const uint16_t hi = Cvt<T16>::one(bv);
+        q = kp == kbias ? hi : Cvt<T16>::one(bv - Cvt<T16>::back(hi));
+    } else if (row < out) {
         if (nfeat == 0) {
             if (kp < in) q = Cvt<T16>::one(W[(size_t)row * in + kp]);
         } else if (kp < nfeat) {
@@ -120,75 +137,98 @@ __device__ __forceinline__ void store_coord_chunks(uint32_t addr0, uint32_t addr
                    zl = Cvt<T16>::one(z - Cvt<T16>::back(zh));
     st_shared_v4(addr0, xh | ((uint32_t)yh << 16), zh | ((uint32_t)xh << 16), yh | ((uint32_t)zh << 16),
                  xl | ((uint32_t)yl << 16));
-    st_shared_v4(addr1, zl, 0u, 0u, 0u);
+    const uint32_t one = Cvt<T16>::one(1.0f);
+    st_shared_v4(addr1, zl | (one << 16), one, 0u, 0u);          // [z_lo, 1, 1, 0 ...]: the ones meet [b_hi, b_lo]
 }
 
 // ---------------------------------------------------------------- shared epilogue pieces
-// Hidden-layer epilogue of one thread (= one tile row): TMEM accumulators [ncols] -> +bias, ReLU -> 16-bit ->
-// the row's 16-byte vectors of the next layer's A/B operand tile.  taddr already contains the warp's lane offset.
+// Hidden-layer epilogue of one thread (= one tile row): TMEM accumulators [ncols] (bias already inside, see
+// pack_tile_kernel) -> ReLU + round to 16 bits in ONE instruction per pair -> the row's 16-byte vectors of the next
+// layer's A/B operand tile.  taddr already contains the warp's lane offset.
 template <typename T16>
-__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int c_begin, int c_end,
-                                                const float *__restrict__ bias_s, uint32_t act_row_addr) {
+__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, int c_begin, int c_end, uint32_t act_row_addr) {
     for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         uint32_t v[32];
         ptx::tmem_ld32(taddr + c0, v);
         ptx::tmem_ld_wait();
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            uint32_t p[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int c = q * 8 + e * 2;
-                float a = fmaxf(__uint_as_float(v[c]) + bias_s[c0 + c], 0.f);
-                float b = fmaxf(__uint_as_float(v[c + 1]) + bias_s[c0 + c + 1], 0.f);
-                p[e] = Cvt<T16>::pack(a, b);
-            }
-            st_shared_v4(act_row_addr + (uint32_t)((c0 >> 3) + q) * TC_LBO, p[0], p[1], p[2], p[3]);
-        }
+        for (int q = 0; q < 4; ++q)
+            st_shared_v4(act_row_addr + (uint32_t)((c0 >> 3) + q) * TC_LBO,
+                         Cvt<T16>::pack_relu(v[q * 8 + 0], v[q * 8 + 1]), Cvt<T16>::pack_relu(v[q * 8 + 2], v[q * 8 + 3]),
+                         Cvt<T16>::pack_relu(v[q * 8 + 4], v[q * 8 + 5]), Cvt<T16>::pack_relu(v[q * 8 + 6], v[q * 8 + 7]));
     }
+}
+// the two chunks after a layer's `width` output columns: [1, 1, 0 ...] against the next layer's [b_hi, b_lo, 0 ...]
+template <typename T16>
+__device__ __forceinline__ void store_ones_chunks(uint32_t act_row_addr, int width) {
+    const uint32_t one = Cvt<T16>::one(1.0f);
+    st_shared_v4(act_row_addr + (uint32_t)(width >> 3) * TC_LBO, one | (one << 16), 0u, 0u, 0u);
+    st_shared_v4(act_row_addr + (uint32_t)((width >> 3) + 1) * TC_LBO, 0u, 0u, 0u, 0u);
 }
 
 // Last flow layer (transposed): this thread's TMEM lane is one output channel, the 128 columns are the tile rows
 // (groups of k neighbours).  Radius-masked max per group, + bias, ReLU, store.  KC > 0: k known at compile time, the
 // group bookkeeping folds away and the per-group maxima become independent chains.
-template <int KC>
+template <int KC, typename T16>
 __device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&mk)[4], int k_rt, int g, int nvalid,
-                                               float bias, float *__restrict__ out, int ld) {
+                                               float bias, uint16_t *__restrict__ out, float *__restrict__ out32,
+                                               int ld) {
     const int k = KC ? KC : k_rt;
     float cur = -INFINITY;
     int cnt = 0, og = 0;
-#pragma unroll
-    for (int c0 = 0; c0 < 128; c0 += 32) {
-        uint32_t v[32];
-        ptx::tmem_ld32(taddr + c0, v);
-        ptx::tmem_ld_wait();
-        const uint32_t mword = mk[c0 >> 5];
+    auto consume = [&](const uint32_t (&v)[32], uint32_t mword) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
             const float x = ((mword >> i) & 1u) ? -INFINITY : __uint_as_float(v[i]);
             cur = fmaxf(cur, x);
             if (++cnt == k) {
-                if (og < g && og < nvalid) out[(size_t)og * ld] = fmaxf(cur + bias, 0.f);
+                if (og < g && og < nvalid) {
+                    const float val = fmaxf(cur + bias, 0.f);
+                    out[(size_t)og * ld] = Cvt<T16>::one(val);
+                    if (out32) out32[(size_t)og * ld] = val;
+                }
                 ++og; cnt = 0; cur = -INFINITY;
             }
         }
+    };
+    // two TMEM loads in flight per wait
+#pragma unroll
+    for (int c0 = 0; c0 < 128; c0 += 64) {
+        uint32_t v0[32], v1[32];
+        ptx::tmem_ld32(taddr + c0, v0);
+        ptx::tmem_ld32(taddr + c0 + 32, v1);
+        ptx::tmem_ld_wait();
+        consume(v0, mk[c0 >> 5]);
+        consume(v1, mk[(c0 >> 5) + 1]);
     }
 }
 
 // ---------------------------------------------------------------- flow embedding
+#ifdef DCLR_TRACE
+// tools/head_trace.py: SM-clock timestamps of CTA 0's roles (build -DDCLR_TRACE only)
+__device__ long long g_trace[1024];
+__device__ long long g_flow_trace[1024];
+#define FLTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && q == 0 && half == 0 && s == 0 && ft < 8) g_flow_trace[ft * 16 + (slot)] = clock64(); } while (0)
+#define TRACE(slot) do { if (blockIdx.x == 0 && (slot) < 1024) g_trace[(slot)] = clock64(); } while (0)
+#else
+#define FLTRACE(slot) do { } while (0)
+#define TRACE(slot) do { } while (0)
+#endif
 struct FlowArgs {
     const float *xyz;       // [2B, n, 3] sampled coordinates, templates first
-    const float *feat;      // [2B, n, F] point-major set-abstraction features
+    const uint16_t *feat;   // [2B, n, F] point-major set-abstraction features, 16-bit operand format
     const int32_t *nbr;     // [B, n, k] source index (local to the pair) of the k nearest source samples
     const uint16_t *w;      // packed images: W1 [128 x K0p] | W2 [128 x 128] | W3 [H3 x 128] (128-row blocks)
     const float *bias;      // b1[128] b2[128] b3[H3]
-    float *out;             // [B*n, H3] motion features (coordinates are kept in xyz)
+    uint16_t *out;          // [B*n, H3] motion features, 16-bit (coordinates are kept in xyz)
+    float *out32;           // same in fp32 for the API tap, or null
     int B, n, k, F, K0p, H3;
     float radius;
     int groups_per_tile, tiles_per_pair, num_tiles;
 };
 
 constexpr int FLOW_SLOTS = 2;
+constexpr int FLOW_K2P = 128 + 16;     // layer-2 K: 128 hidden + [b_hi, b_lo, 0 ...] against the ones chunks
 constexpr int FLOW_WPS = 8;           // build/epilogue warps per slot: 4 TMEM lane quarters x 2 column halves
 constexpr int FLOW_MMA_WARP = FLOW_SLOTS * FLOW_WPS;
 constexpr int FLOW_THREADS = (FLOW_MMA_WARP + 1) * 32;
@@ -199,7 +239,7 @@ flow_tc_kernel(FlowArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int K0p = a.K0p, H3 = a.H3;
-    const uint32_t w1_bytes = 128u * K0p * 2, w2_bytes = 128u * 128 * 2, w3_bytes = (uint32_t)H3 * 128 * 2;
+    const uint32_t w1_bytes = 128u * K0p * 2, w2_bytes = 128u * FLOW_K2P * 2, w3_bytes = (uint32_t)H3 * 128 * 2;
     const uint32_t act_bytes = 128u * K0p * 2;
     uint8_t *s_w1 = smem, *s_w2 = s_w1 + w1_bytes, *s_w3 = s_w2 + w2_bytes;
     uint8_t *s_act = s_w3 + w3_bytes;                                    // FLOW_SLOTS x act_bytes
@@ -252,7 +292,7 @@ flow_tc_kernel(FlowArgs a) {
                                 ptx::mma_f16_ss(dcol, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
                                                 make_sdesc(w1a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
                         } else if (layer == 1) {
-                            for (int ks = 0; ks < 8; ++ks)
+                            for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
                                 ptx::mma_f16_ss(dcol + 128, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
                                                 make_sdesc(w2a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
                         } else {
@@ -281,7 +321,10 @@ flow_tc_kernel(FlowArgs a) {
         const int k = a.k, n = a.n, F = a.F, g = a.groups_per_tile;
         const int fc = F / 8;                                          // chunks per feature block
         uint32_t dphase = 0;
+        [[maybe_unused]] int ft = -1;
         for (int tile = blockIdx.x * FLOW_SLOTS + s; tile < a.num_tiles; tile += tiles_per_iter) {
+            ++ft;
+            FLTRACE(0);
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * g;
             // ---- build row r = (point p0 + r / k, neighbour r % k): [f_tmpl | f_src | dp hi,hi,lo | 0]
@@ -294,12 +337,12 @@ flow_tc_kernel(FlowArgs a) {
                 const int src = __ldg(a.nbr + trow * k + j);
                 const size_t srow = (size_t)(a.B + b) * n + src;
                 if (half == 0) {
-                    const float4 *ft = reinterpret_cast<const float4 *>(a.feat + trow * F);
-#pragma unroll 4
+                    // 16-bit features are already operand bytes: one 16-byte chunk per load, all chunks in flight
+                    const uint4 *ft = reinterpret_cast<const uint4 *>(a.feat + trow * F);
+#pragma unroll 8
                     for (int c = 0; c < fc; ++c) {
-                        const float4 u0 = __ldg(ft + 2 * c), u1 = __ldg(ft + 2 * c + 1);
-                        st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
-                                     Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
+                        const uint4 u = __ldg(ft + c);
+                        st_shared_v4(act_row + c * TC_LBO, u.x, u.y, u.z, u.w);
                     }
                     const float *pt3 = a.xyz + trow * 3, *ps3 = a.xyz + srow * 3;
                     const float dx = __ldg(ps3) - __ldg(pt3), dy = __ldg(ps3 + 1) - __ldg(pt3 + 1),
@@ -308,12 +351,11 @@ flow_tc_kernel(FlowArgs a) {
                     // radius mask in fp32 on the raw displacement (deepclr.py:220-222)
                     masked = a.radius > 0.f && sqrtf(dx * dx + dy * dy + dz * dz) >= a.radius;
                 } else {
-                    const float4 *fs = reinterpret_cast<const float4 *>(a.feat + srow * F);
-#pragma unroll 4
+                    const uint4 *fs = reinterpret_cast<const uint4 *>(a.feat + srow * F);
+#pragma unroll 8
                     for (int c = 0; c < fc; ++c) {
-                        const float4 v0 = __ldg(fs + 2 * c), v1 = __ldg(fs + 2 * c + 1);
-                        st_shared_v4(act_row + (fc + c) * TC_LBO, Cvt<T16>::pack(v0.x, v0.y),
-                                     Cvt<T16>::pack(v0.z, v0.w), Cvt<T16>::pack(v1.x, v1.y), Cvt<T16>::pack(v1.z, v1.w));
+                        const uint4 u = __ldg(fs + c);
+                        st_shared_v4(act_row + (fc + c) * TC_LBO, u.x, u.y, u.z, u.w);
                     }
                     for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
                 }
@@ -332,37 +374,47 @@ flow_tc_kernel(FlowArgs a) {
                 if (lane == 0) s_maskw[s * 4 + q] = mw;
             }
             ptx::fence_proxy_async_smem();
+            FLTRACE(1);
             ptx::mbar_arrive(&ready[s]);
             // ---- layer 1 epilogue -> H1 (in place of the rows)
             ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
             ptx::tc_fence_after();
-            epilogue_hidden<T16>(tlane, half * 64, half * 64 + 64, s_bias, act_row);
+            FLTRACE(2);
+            epilogue_hidden<T16>(tlane, half * 64, half * 64 + 64, act_row);
+            if (half == 1) store_ones_chunks<T16>(act_row, 128);       // layer 2's bias columns (K 128..143)
             ptx::tc_fence_before();
             ptx::fence_proxy_async_smem();
+            FLTRACE(3);
             ptx::mbar_arrive(&ready[s]);
             // ---- layer 2 epilogue -> H2
             ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
             ptx::tc_fence_after();
-            epilogue_hidden<T16>(tlane + 128, half * 64, half * 64 + 64, s_bias + 128, act_row);
+            FLTRACE(4);
+            epilogue_hidden<T16>(tlane + 128, half * 64, half * 64 + 64, act_row);
             ptx::tc_fence_before();
             ptx::fence_proxy_async_smem();
+            FLTRACE(5);
             ptx::mbar_arrive(&ready[s]);
             // ---- layer 3 epilogue (transposed): lane = output channel, columns = tile rows; max over each group
             ptx::mbar_wait(&done[s], dphase & 1); ++dphase;
             ptx::tc_fence_after();
+            FLTRACE(6);
             uint32_t mk[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) mk[i] = s_maskw[s * 4 + i];
             for (int mb = half; mb < H3 / 128; mb += 2) {
                 const int ch = mb * 128 + r;
                 const float bias = s_bias[256 + ch];
-                float *out = a.out + ((size_t)b * n + p0) * H3 + ch;
+                const size_t o0 = ((size_t)b * n + p0) * H3 + ch;
+                uint16_t *out = a.out + o0;
+                float *out32 = a.out32 ? a.out32 + o0 : nullptr;
                 const uint32_t ta = tlane + mb * 128;
-                if (k == 20) flow_group_max<20>(ta, mk, k, g, n - p0, bias, out, H3);
-                else if (k == 30) flow_group_max<30>(ta, mk, k, g, n - p0, bias, out, H3);
-                else flow_group_max<0>(ta, mk, k, g, n - p0, bias, out, H3);
+                if (k == 20) flow_group_max<20, T16>(ta, mk, k, g, n - p0, bias, out, out32, H3);
+                else if (k == 30) flow_group_max<30, T16>(ta, mk, k, g, n - p0, bias, out, out32, H3);
+                else flow_group_max<0, T16>(ta, mk, k, g, n - p0, bias, out, out32, H3);
             }
             ptx::tc_fence_before();
+            FLTRACE(7);
         }
     }
     __syncthreads();
@@ -370,13 +422,6 @@ flow_tc_kernel(FlowArgs a) {
 }
 
 // ---------------------------------------------------------------- output head
-#ifdef DCLR_TRACE
-// tools/head_trace.py: SM-clock timestamps of CTA 0's roles (build -DDCLR_TRACE only)
-__device__ long long g_trace[1024];
-#define TRACE(slot) do { if (blockIdx.x == 0 && (slot) < 1024) g_trace[(slot)] = clock64(); } while (0)
-#else
-#define TRACE(slot) do { } while (0)
-#endif
 constexpr int HEAD_LAYERS = 5;
 constexpr int HEAD_KT = 64;                      // K elements per streamed weight tile (128 rows x 64 = 16 KB)
 constexpr int HEAD_STAGES = 5;
@@ -386,7 +431,7 @@ constexpr int HEAD_PROD_WARP = HEAD_EPI_WARPS, HEAD_MMA_WARP = HEAD_EPI_WARPS + 
 constexpr int HEAD_THREADS = (HEAD_EPI_WARPS + 2) * 32;
 
 struct HeadArgs {
-    const float *feat;      // [B*n, C0] motion features
+    const uint16_t *feat;   // [B*n, C0] motion features, 16-bit operand format
     const float *xyz;       // [B*n, 3] template sample coordinates
     const uint16_t *w;      // packed weight tiles in (layer, 128-row block, K block) order
     const float *bias;      // biases of the 5 layers, concatenated
@@ -502,19 +547,18 @@ head_tc_kernel(HeadArgs a) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * 128;
             const int pt = p0 + r;
-            const int tr0 = ((tile - blockIdx.x) / gridDim.x) * 64 + 16;
+            [[maybe_unused]] const int tr0 = ((tile - blockIdx.x) / gridDim.x) * 64 + 16;
             if (tid == 0) TRACE(tr0);
             // ---- input rows: [motion feat (C0) | xyz hi,hi,lo | 0]; half 0 writes the first feature chunks, half 1
             //      the rest, the coordinates and the padding
             const int cb = half == 0 ? 0 : cmid, ce = half == 0 ? cmid : cc;
             if (pt < n) {
                 const size_t row = (size_t)b * n + pt;
-                const float4 *f = reinterpret_cast<const float4 *>(a.feat + row * C0);
-#pragma unroll 4
+                const uint4 *f = reinterpret_cast<const uint4 *>(a.feat + row * C0);
+#pragma unroll 8
                 for (int c = cb; c < ce; ++c) {
-                    const float4 u0 = __ldg(f + 2 * c), u1 = __ldg(f + 2 * c + 1);
-                    st_shared_v4(act_row + c * TC_LBO, Cvt<T16>::pack(u0.x, u0.y), Cvt<T16>::pack(u0.z, u0.w),
-                                 Cvt<T16>::pack(u1.x, u1.y), Cvt<T16>::pack(u1.z, u1.w));
+                    const uint4 u = __ldg(f + c);
+                    st_shared_v4(act_row + c * TC_LBO, u.x, u.y, u.z, u.w);
                 }
                 if (half == 1) {
                     const float *p3 = a.xyz + row * 3;
@@ -537,7 +581,8 @@ head_tc_kernel(HeadArgs a) {
                 ptx::tc_fence_after();
                 if (tid == 0) TRACE(tr0 + 2 + l * 2);
                 const int hw = a.out[l] / 2;
-                epilogue_hidden<T16>(tlane, half * hw, half * hw + hw, s_bias + boff, act_row);
+                epilogue_hidden<T16>(tlane, half * hw, half * hw + hw, act_row);
+                if (half == 1 && l < HEAD_LAYERS - 2) store_ones_chunks<T16>(act_row, a.out[l]);   // next layer's bias
                 boff += a.out[l];
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async_smem();
@@ -594,19 +639,24 @@ struct TcModel {
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 template <typename T16>
-static int pack_rows(const float *W, int out, int in, int nfeat, int row0, int R, int k0, int Kt, uint16_t *dst) {
-    pack_tile_kernel<T16><<<div_up(R * Kt, 256), 256>>>(W, out, in, nfeat, row0, R, k0, Kt, dst);
+static int pack_rows(const float *W, const float *bias, int kbias, int out, int in, int nfeat, int row0, int R, int k0,
+                     int Kt, uint16_t *dst) {
+    pack_tile_kernel<T16><<<div_up(R * Kt, 256), 256>>>(W, bias, kbias, out, in, nfeat, row0, R, k0, Kt, dst);
     DCLR_LAUNCH_CHECK("pack_tile_kernel");
     return DCLR_OK;
 }
 
-static int pack_any(int fmt, const float *W, int out, int in, int nfeat, int row0, int R, int k0, int Kt,
+static int pack_any(int fmt, const float *W, const float *bias, int kbias, int out, int in, int nfeat, int row0, int R,
+                    int k0, int Kt,
                     uint16_t *dst) {
-    return fmt == 1 ? pack_rows<__nv_bfloat16>(W, out, in, nfeat, row0, R, k0, Kt, dst)
-                    : pack_rows<__half>(W, out, in, nfeat, row0, R, k0, Kt, dst);
+    return fmt == 1 ? pack_rows<__nv_bfloat16>(W, bias, kbias, out, in, nfeat, row0, R, k0, Kt, dst)
+                    : pack_rows<__half>(W, bias, kbias, out, in, nfeat, row0, R, k0, Kt, dst);
 }
 
 #ifdef DCLR_TRACE
+extern "C" int dclr_debug_read_flow_trace(long long *dst, int n) {
+    return cudaMemcpyFromSymbol(dst, g_flow_trace, sizeof(long long) * (n < 1024 ? n : 1024)) == cudaSuccess ? 0 : -1;
+}
 extern "C" int dclr_debug_read_trace(long long *dst, int n) {
     return cudaMemcpyFromSymbol(dst, g_trace, sizeof(long long) * (n < 1024 ? n : 1024)) == cudaSuccess ? 0 : -1;
 }
@@ -639,7 +689,7 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     TcModel *t = new (std::nothrow) TcModel();
     if (!t) return fail(DCLR_E_INVALID, "out of host memory");
     t->fmt = fmt; t->F = F; t->k = k; t->radius = radius; t->H3 = H3;
-    t->K0p = round_up(2 * F + 9, 16);
+    t->K0p = round_up(2 * F + 9 + 2, 16);          // features | 9 coordinate columns | 2 bias columns
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&t->num_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -653,20 +703,20 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     } while (0)
 
     // ---- flow: W1 [128 x K0p] | W2 [128 x 128] | W3 in 128-row blocks [H3 x 128]; biases b1 b2 b3
-    const size_t flow_elems = (size_t)128 * t->K0p + 128 * 128 + (size_t)H3 * 128;
+    const size_t flow_elems = (size_t)128 * t->K0p + 128 * FLOW_K2P + (size_t)H3 * 128;
     TC_CUDA(cudaMalloc(&t->flow_w, flow_elems * 2));
     TC_CUDA(cudaMalloc(&t->flow_b, (256 + H3) * sizeof(float)));
     uint16_t *p = t->flow_w;
-    if ((rc = pack_any(fmt, sp[0].W, 128, sp[0].in, 2 * F, 0, 128, 0, t->K0p, p))) return bail(rc);
+    if ((rc = pack_any(fmt, sp[0].W, sp[0].b, 2 * F + 9, 128, sp[0].in, 2 * F, 0, 128, 0, t->K0p, p))) return bail(rc);
     p += (size_t)128 * t->K0p;
-    if ((rc = pack_any(fmt, sp[1].W, 128, 128, 0, 0, 128, 0, 128, p))) return bail(rc);
-    p += 128 * 128;
+    if ((rc = pack_any(fmt, sp[1].W, sp[1].b, 128, 128, 128, 0, 0, 128, 0, FLOW_K2P, p))) return bail(rc);
+    p += 128 * FLOW_K2P;
     for (int mb = 0; mb < H3 / 128; ++mb, p += 128 * 128)
-        if ((rc = pack_any(fmt, sp[2].W, H3, 128, 0, mb * 128, 128, 0, 128, p))) return bail(rc);
+        if ((rc = pack_any(fmt, sp[2].W, nullptr, 0, H3, 128, 0, mb * 128, 128, 0, 128, p))) return bail(rc);
     TC_CUDA(cudaMemcpy(t->flow_b, sp[0].b, 128 * 4, cudaMemcpyDeviceToDevice));
     TC_CUDA(cudaMemcpy(t->flow_b + 128, sp[1].b, 128 * 4, cudaMemcpyDeviceToDevice));
     TC_CUDA(cudaMemcpy(t->flow_b + 256, sp[2].b, H3 * 4, cudaMemcpyDeviceToDevice));
-    t->flow_smem = (size_t)128 * t->K0p * 2 + 128 * 128 * 2 + (size_t)H3 * 128 * 2 +
+    t->flow_smem = (size_t)128 * t->K0p * 2 + 128 * FLOW_K2P * 2 + (size_t)H3 * 128 * 2 +
                    (size_t)FLOW_SLOTS * 128 * t->K0p * 2 + (256 + H3) * 4 + FLOW_SLOTS * 4 * 4 +
                    (1 + 2 * FLOW_SLOTS) * 8 + 16;
 
@@ -675,7 +725,9 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     int nbias = 0;
     t->head_act_k = 0;
     for (int l = 0; l < HEAD_LAYERS; ++l) {
-        t->head_Kp[l] = round_up(l == 0 ? H3 + 9 : sp[3 + l].in, 16);
+        // hidden layers carry their bias as two extra K columns (l = 0: in the coordinate padding); the last layer adds
+        // it in the epilogue, in fp32
+        t->head_Kp[l] = l == 0 ? round_up(H3 + 9 + 2, 16) : (l < HEAD_LAYERS - 1 ? sp[3 + l].in + 16 : sp[3 + l].in);
         t->head_out[l] = sp[3 + l].out;
         head_elems += (size_t)t->head_out[l] * t->head_Kp[l];
         nbias += t->head_out[l];
@@ -691,7 +743,9 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
         for (int nc = 0; nc < s.out / 128; ++nc)
             for (int k0 = 0; k0 < t->head_Kp[l]; k0 += HEAD_KT) {
                 const int kt = t->head_Kp[l] - k0 < HEAD_KT ? t->head_Kp[l] - k0 : HEAD_KT;
-                if ((rc = pack_any(fmt, s.W, s.out, s.in, l == 0 ? H3 : 0, nc * 128, 128, k0, kt, p))) return bail(rc);
+                if ((rc = pack_any(fmt, s.W, l < HEAD_LAYERS - 1 ? s.b : nullptr, l == 0 ? H3 + 9 : s.in, s.out, s.in,
+                                   l == 0 ? H3 : 0, nc * 128, 128, k0, kt, p)))
+                    return bail(rc);
                 p += (size_t)128 * kt;
             }
         TC_CUDA(cudaMemcpy(t->head_b + boff, s.b, s.out * 4, cudaMemcpyDeviceToDevice));
@@ -719,10 +773,25 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     return DCLR_OK;
 }
 
-int tc_flow(TcModel *t, const float *xyz, const float *feat, const int32_t *nbr, int B, int n, float *motion,
-            cudaStream_t st) {
+template <typename T16>
+__global__ void convert16_kernel(const float *__restrict__ src, uint16_t *__restrict__ dst, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        dst[i] = Cvt<T16>::one(__ldg(src + i));
+}
+
+int tc_convert(TcModel *t, const float *src, uint16_t *dst, size_t n, cudaStream_t st) {
+    const int grid = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+    if (t->fmt == 1) convert16_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(src, dst, n);
+    else convert16_kernel<__half><<<grid, 256, 0, st>>>(src, dst, n);
+    DCLR_LAUNCH_CHECK("convert16_kernel");
+    return DCLR_OK;
+}
+
+int tc_flow(TcModel *t, const float *xyz, const uint16_t *feat, const int32_t *nbr, int B, int n, uint16_t *motion,
+            float *motion32, cudaStream_t st) {
     FlowArgs fa;
     fa.xyz = xyz; fa.feat = feat; fa.nbr = nbr; fa.w = t->flow_w; fa.bias = t->flow_b; fa.out = motion;
+    fa.out32 = motion32;
     fa.B = B; fa.n = n; fa.k = t->k; fa.F = t->F; fa.K0p = t->K0p; fa.H3 = t->H3; fa.radius = t->radius;
     fa.groups_per_tile = 128 / t->k;
     fa.tiles_per_pair = div_up(n, fa.groups_per_tile);
@@ -734,7 +803,7 @@ int tc_flow(TcModel *t, const float *xyz, const float *feat, const int32_t *nbr,
     return DCLR_OK;
 }
 
-int tc_head(TcModel *t, const float *xyz, const float *motion, int B, int n, float *pooled, cudaStream_t st) {
+int tc_head(TcModel *t, const float *xyz, const uint16_t *motion, int B, int n, float *pooled, cudaStream_t st) {
     HeadArgs ha;
     ha.feat = motion; ha.xyz = xyz; ha.w = t->head_w; ha.bias = t->head_b; ha.pooled = pooled;
     ha.B = B; ha.n = n; ha.C0 = t->H3;

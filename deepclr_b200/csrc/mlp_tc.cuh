@@ -12,12 +12,15 @@ struct TcModel;
 // fmt: 1 = bf16, 2 = fp16 operands (fp32 accumulation either way)
 int tc_create(const TcLayerSpec *specs, int F, int k, float radius, int fmt, TcModel **out);
 void tc_destroy(TcModel *t);
-// xyz [2B,n,3], feat [2B,n,F] point-major (templates first), nbr [B,n,k] -> motion [B*n, merge_out] features only
-// (the coordinates stay in xyz)
-int tc_flow(TcModel *t, const float *xyz, const float *feat, const int32_t *nbr, int B, int n, float *motion,
-            cudaStream_t st);
-// motion [B*n, merge_out] + xyz [B*n,3] -> pooled [B, C_last] (max over the points); zero-fills pooled first
-int tc_head(TcModel *t, const float *xyz, const float *motion, int B, int n, float *pooled, cudaStream_t st);
+// All activations that cross kernels are 16-bit images in the model's operand format (fp16 / bf16):
+// xyz [2B,n,3] fp32, feat16 [2B,n,F] point-major (templates first), nbr [B,n,k] -> motion16 [B*n, merge_out] features
+// only (the coordinates stay in xyz); motion32 (nullable) additionally receives the fp32 values for the API tap.
+int tc_flow(TcModel *t, const float *xyz, const uint16_t *feat16, const int32_t *nbr, int B, int n, uint16_t *motion16,
+            float *motion32, cudaStream_t st);
+// motion16 [B*n, merge_out] + xyz [B*n,3] -> pooled [B, C_last] (max over the points); zero-fills pooled first
+int tc_head(TcModel *t, const float *xyz, const uint16_t *motion16, int B, int n, float *pooled, cudaStream_t st);
+// fp32 -> the model's 16-bit format, elementwise (features supplied by the caller: dclr_forward_features)
+int tc_convert(TcModel *t, const float *src, uint16_t *dst, size_t n, cudaStream_t st);
 int tc_format(const TcModel *t);
 
 }  // namespace dclr

@@ -24,6 +24,7 @@ struct dclr_model {
     void *bq_ws, *fps_ws;
     float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
     uint8_t *mask;
+    uint16_t *sa_feat16, *motion16;  // 16-bit images of sa_feat / motion for the tensor-core stages
     dclr::TcModel *tc = nullptr;     // bf16 tensor-core path (mlp_tc.cu)
     // optional per-stage CUDA-event timing (dclr_model_set_timing): ring of calls x (stages + 1) events
     bool timing = false;
@@ -73,9 +74,12 @@ static size_t carve(dclr_model *m, char *base, int G, int N, int B) {
         m->mask = (uint8_t *)take(R);
         m->actA = (float *)take(BM * wmax * 4);
         m->actB = (float *)take(BM * wmax * 4);
+        m->sa_feat16 = m->motion16 = nullptr;
     } else {
         m->rows = m->h1 = m->h2 = m->h3 = m->actA = m->actB = nullptr;
         m->mask = nullptr;
+        m->sa_feat16 = (uint16_t *)take((size_t)G * M * m->F * 2);
+        m->motion16 = (uint16_t *)take(BM * a.merge_mlp[2] * 2);
     }
     return off;
 }
@@ -150,6 +154,8 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     SaArgs s;
     s.x = x; s.new_xyz = m->new_xyz; s.N = N; s.M = a.npoint; s.ld_out = m->F; s.nscales = a.num_scales;
     s.out = m->sa_feat;
+    s.out16 = m->numerics != 0 ? m->sa_feat16 : nullptr;
+    s.fmt16 = m->numerics;
     for (int i = 0; i < 2; ++i) {
         s.idx[i] = m->bq_idx[i]; s.cnt[i] = m->bq_cnt[i]; s.ns[i] = a.nsamples[i < a.num_scales ? i : 0];
         s.w_host[i] = m->sa_w_host[i < a.num_scales ? i : 0].data();
@@ -172,10 +178,12 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     if (m->numerics != 0) {
         {
             StageScope sc(m, ST_FLOW, st);
-            DCLR_TRY(tc_flow(m->tc, m->new_xyz, m->sa_feat, m->knn_col, B, M, m->motion, st));
+            // fp32 motion features only when the caller taps them; the head reads the 16-bit image
+            DCLR_TRY(tc_flow(m->tc, m->new_xyz, m->sa_feat16, m->knn_col, B, M, m->motion16,
+                             motion_out ? m->motion : nullptr, st));
         }
         StageScope sc(m, ST_HEAD, st);
-        DCLR_TRY(tc_head(m->tc, m->new_xyz, m->motion, B, M, m->pooled, st));
+        DCLR_TRY(tc_head(m->tc, m->new_xyz, m->motion16, B, M, m->pooled, st));
     } else {
         timing_mark(m, ST_FLOW, 0, st);
         const int ld0 = (int)align_up(m->nmerge_in, 4);
@@ -358,6 +366,8 @@ extern "C" int dclr_forward_features(dclr_model *m, const float *feat, int B, fl
     {
         StageScope sc(m, ST_LAYOUT, st);
         DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, st));
+        if (m->numerics != 0)
+            DCLR_TRY(tc_convert(m->tc, m->sa_feat, m->sa_feat16, (size_t)2 * B * m->arch.npoint * m->F, st));
     }
     return run_merge_output(m, B, y_out, motion_out, st);
 }

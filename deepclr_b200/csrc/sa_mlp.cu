@@ -14,6 +14,8 @@
 // coalesced 128-byte store.  The 1.7 KB of weights per scale live in the kernel parameter block (constant bank), so an
 // FFMA reads its weight as a constant operand instead of through a shared-memory load.
 #include "common.cuh"
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include "kernels.cuh"
 
 namespace dclr {
@@ -28,7 +30,8 @@ struct SaParams {
     const int32_t *cnt[2];   // [B,M]
     int ns[2];
     float *out;              // [B,M,ld_out] point-major; scale s writes columns [s*32, (s+1)*32)
-    int N, M, ld_out, nscales;
+    uint16_t *out16;         // same layout as fp16 (fmt16 = 2) / bf16 (fmt16 = 1) for the tensor-core stages, or null
+    int N, M, ld_out, nscales, fmt16;
     float w[2][SA_WMAX];     // per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
 };
 
@@ -127,7 +130,11 @@ sa_mlp_kernel(const __grid_constant__ SaParams a) {
                 cur = fmaxf(cur, tile[r][lane]);
                 if ((lastmask >> r) & 1u) {
                     // centres without rows do not exist below a.M, so finished centres are consecutive
-                    a.out[((size_t)b * a.M + c0 + done) * a.ld_out + s * H3 + lane] = cur;
+                    const size_t o = ((size_t)b * a.M + c0 + done) * a.ld_out + s * H3 + lane;
+                    a.out[o] = cur;
+                    if (a.out16)
+                        a.out16[o] = a.fmt16 == 1 ? __bfloat16_as_ushort(__float2bfloat16_rn(cur))
+                                                  : __half_as_ushort(__float2half_rn(cur));
                     cur = 0.f;
                     ++done;
                 }
@@ -141,7 +148,7 @@ int sa_mlp_launch(const SaArgs &s, int B, int cin, const int *h, cudaStream_t st
         return fail(DCLR_E_UNSUPPORTED, "sa_mlp: only mlp [16,16,32] is built (got [%d,%d,%d])", h[0], h[1], h[2]);
     if (cin != 3 && cin != 4) return fail(DCLR_E_UNSUPPORTED, "sa_mlp: input_dim must be 3 or 4 (got %d)", cin);
     SaParams p;
-    p.x = s.x; p.new_xyz = s.new_xyz; p.out = s.out; p.N = s.N; p.M = s.M; p.ld_out = s.ld_out; p.nscales = s.nscales;
+    p.x = s.x; p.new_xyz = s.new_xyz; p.out = s.out; p.out16 = s.out16; p.fmt16 = s.fmt16; p.N = s.N; p.M = s.M; p.ld_out = s.ld_out; p.nscales = s.nscales;
     const int wsz = cin * 16 + 16 + 16 * 16 + 16 + 32 * 16 + 32;
     for (int i = 0; i < 2; ++i) {
         p.idx[i] = s.idx[i]; p.cnt[i] = s.cnt[i]; p.ns[i] = s.ns[i];

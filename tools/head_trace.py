@@ -34,3 +34,14 @@ for tile in range(4):
             line += f' | epilogue {rel(18 + 2 * l)}..{rel(19 + 2 * l)}'
         print(line)
     print('  fin blocks done at', [rel(26 + nc) for nc in range(8)])
+
+fn2 = _lib.lib().dclr_debug_read_flow_trace
+fn2.argtypes = [ctypes.c_void_p, ctypes.c_int]
+assert fn2(buf, 1024) == 0
+f = np.array(buf[:128], dtype=np.int64).reshape(8, 16)
+print('flow slot 0 of CTA 0, per tile: build | wait L1 | epi1 | wait L2 | epi2 | wait L3 | epi3 | total   (cycles)')
+for i in range(8):
+    x = f[i]
+    if x[0] == 0:
+        continue
+    print(i, [int(x[j + 1] - x[j]) for j in range(7)], int(x[7] - x[0]), 'gap to next', int(f[i + 1][0] - x[7]) if i < 7 else '-')
