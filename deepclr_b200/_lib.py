@@ -9,7 +9,8 @@ import subprocess
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libdeepclr_b200.so')
+# DCLR_LIB: an alternative build of the same library (A/B kernel experiments, tools/ab.sh); default = the in-tree build
+LIB_PATH = os.environ.get('DCLR_LIB') or os.path.join(_HERE, 'libdeepclr_b200.so')
 _lib = None
 
 c_int, c_float, c_void_p, c_size_t = ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_size_t

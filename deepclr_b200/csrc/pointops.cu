@@ -360,6 +360,32 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
         }
         (void)lt_mask;
         const size_t o0 = gy * k;
+        if (total <= 64) {                                      // warp-uniform; the usual case (~1.5 k survivors)
+            // rank by counting: keys are unique (index in the low word), so #(keys smaller than mine) is my place in
+            // the ascending (d2, index) order -- one broadcast shared-memory read per survivor instead of k ordered
+            // extractions with two 64-bit warp reductions each
+            int r0 = 0, r1 = 0;
+#pragma unroll 4
+            for (int j = 0; j < total; ++j) {
+                const uint64_t kj = cand[j];
+                r0 += kj < c0 ? 1 : 0;
+                r1 += kj < c1 ? 1 : 0;
+            }
+            if (lane < total && r0 < k) {
+                const uint32_t ci = (uint32_t)c0;
+                if (row_out) row_out[o0 + r0] = (int64_t)gy;
+                if (col_out) col_out[o0 + r0] = (int64_t)((size_t)b * Nx + ci);
+                if (col_local) col_local[o0 + r0] = (int32_t)ci;
+            }
+            if (lane + 32 < total && r1 < k) {
+                const uint32_t ci = (uint32_t)c1;
+                if (row_out) row_out[o0 + r1] = (int64_t)gy;
+                if (col_out) col_out[o0 + r1] = (int64_t)((size_t)b * Nx + ci);
+                if (col_local) col_local[o0 + r1] = (int32_t)ci;
+            }
+            __syncwarp();
+            continue;
+        }
         for (int r = 0; r < k; ++r) {
             uint64_t lm;
             if (fits) {
