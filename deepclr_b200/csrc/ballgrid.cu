@@ -19,6 +19,7 @@ namespace dclr {
 constexpr int BG_G = 128;                  // cells per axis
 constexpr int BG_CELLS = BG_G * BG_G;
 constexpr int BG_BUILD_T = 1024;
+constexpr int BG_LIST = 64;                // hits ranked from a list instead of the bitmap scan (2 per lane)
 constexpr int BG_PARAMS = 8;               // floats per cloud: axis0, axis1 (as int bits), o0, o1, inv0, inv1
 
 __device__ __forceinline__ int bg_cell(float v, float o, float inv) {
@@ -154,7 +155,8 @@ __global__ void bq_grid_query_kernel(BgQueryArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int b = blockIdx.y;
     const int words = (a.N + 31) >> 5;
-    uint32_t *bm = s_bm + (size_t)warp * NR * words;
+    uint32_t *bm = s_bm + (size_t)warp * (NR * words + BG_LIST);
+    uint32_t *list = bm + NR * words;
     for (int w = lane; w < NR * words; w += 32) bm[w] = 0u;
     __syncwarp();
     const float *par = a.params + (size_t)b * BG_PARAMS;
@@ -171,19 +173,75 @@ __global__ void bq_grid_query_kernel(BgQueryArgs a) {
         const float R0 = a.rq + fabsf(v0) * 1e-6f, R1 = a.rq + fabsf(v1) * 1e-6f;
         const int x0 = bg_cell(v0 - R0, o0, inv0), x1 = bg_cell(v0 + R0, o0, inv0);
         const int y0 = bg_cell(v1 - R1, o1, inv1), y1 = bg_cell(v1 + R1, o1, inv1);
+        int total = 0;                                  // hits of the widest radius so far (warp-uniform)
         for (int y = y0; y <= y1; ++y) {
             const int beg = __ldg(cs + y * BG_G + x0), end = __ldg(cs + y * BG_G + x1 + 1);
-            for (int t = beg + lane; t < end; t += 32) {
-                const float4 p = __ldg(rec + t);
-                // operand order of the reference: (new - x), ball_query_gpu.cu:33
-                const float d2 = sqdist_pn2(cx - p.x, cy - p.y, cz - p.z);
-                const int k = __float_as_int(p.w);
+            for (int t0 = beg; t0 < end; t0 += 32) {
+                const int t = t0 + lane;
+                bool any = false;
+                uint32_t e = 0u;
+                if (t < end) {
+                    const float4 p = __ldg(rec + t);
+                    // operand order of the reference: (new - x), ball_query_gpu.cu:33
+                    const float d2 = sqdist_pn2(cx - p.x, cy - p.y, cz - p.z);
+                    const int k = __float_as_int(p.w);
+                    e = (uint32_t)k;
 #pragma unroll
-                for (int r = 0; r < NR; ++r)
-                    if (d2 < a.r2[r]) atomicOr(&bm[r * words + (k >> 5)], 1u << (k & 31));
+                    for (int r = 0; r < NR; ++r)
+                        if (d2 < a.r2[r]) {
+                            atomicOr(&bm[r * words + (k >> 5)], 1u << (k & 31));
+                            e |= 0x80000000u >> r;      // membership flags ride in the top bits (N < 2^30)
+                            any = true;
+                        }
+                }
+                // short hit list next to the bitmap: sparse neighbourhoods are ranked from it (below)
+                const unsigned hm = __ballot_sync(0xffffffffu, any);
+                if (hm) {
+                    const int pos = total + __popc(hm & ((1u << lane) - 1u));
+                    if (any && pos < BG_LIST) list[pos] = e;
+                    total += __popc(hm);
+                }
             }
         }
         __syncwarp();
+        if (total <= BG_LIST) {
+            // ---- sparse centre (the usual case on LiDAR scans away from the sensor): the place of a hit in the
+            //      ascending-index order is the number of listed hits of the same radius with a smaller index
+            const uint32_t e0 = lane < total ? list[lane] : 0u, e1 = lane + 32 < total ? list[lane + 32] : 0u;
+            const uint32_t i0 = e0 & 0x3fffffffu, i1 = e1 & 0x3fffffffu;
+            int rk0[NR], rk1[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) rk0[r] = rk1[r] = 0;
+            for (int j = 0; j < total; ++j) {
+                const uint32_t ej = list[j];
+                const uint32_t ij = ej & 0x3fffffffu;
+#pragma unroll
+                for (int r = 0; r < NR; ++r) {
+                    const bool fj = (ej << r) >> 31;
+                    rk0[r] += (fj && ij < i0) ? 1 : 0;
+                    rk1[r] += (fj && ij < i1) ? 1 : 0;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                int32_t *row = a.idx[r] + ((size_t)b * a.M + c) * a.ns[r];
+                const int ns = a.ns[r];
+                const bool f0 = (e0 << r) >> 31, f1 = (e1 << r) >> 31;
+                if (f0) { bm[r * words + (i0 >> 5)] = 0u; if (rk0[r] < ns) row[rk0[r]] = (int32_t)i0; }
+                if (f1) { bm[r * words + (i1 >> 5)] = 0u; if (rk1[r] < ns) row[rk1[r]] = (int32_t)i1; }
+                const int cnt = __popc(__ballot_sync(0xffffffffu, f0)) + __popc(__ballot_sync(0xffffffffu, f1));
+                const int n = min(cnt, ns);
+                if (a.cnt[r] && lane == 0) a.cnt[r][(size_t)b * a.M + c] = n;
+                if (a.pad) {
+                    const uint32_t m0 = f0 ? i0 : 0xffffffffu, m1 = f1 ? i1 : 0xffffffffu;
+                    const uint32_t first = __reduce_min_sync(0xffffffffu, min(m0, m1));
+                    const int fill = n > 0 ? (int)first : 0;
+                    for (int p2 = n + lane; p2 < ns; p2 += 32) row[p2] = fill;
+                }
+            }
+            __syncwarp();
+            continue;
+        }
         // read the bitmaps in index order (and clear them for the next centre)
 #pragma unroll
         for (int r = 0; r < NR; ++r) {
@@ -241,7 +299,7 @@ int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, 
                      cudaStream_t st, int *used) {
     *used = 0;
     const int words = (N + 31) / 32;
-    int warps = (int)((200u * 1024u) / ((size_t)nr * words * 4));
+    int warps = (int)((200u * 1024u) / (((size_t)nr * words + BG_LIST) * 4));
     if (warps > 8) warps = 8;
     if (N < 2048 || warps < 1 || B > 65535) return DCLR_OK;
     float rmax = 0.f;
@@ -270,7 +328,7 @@ int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, 
         a.r2[r] = radii[rr] * radii[rr];            // float radius2 = radius * radius  (ball_query_gpu.cu:23)
         a.ns[r] = ns[rr]; a.idx[r] = idx[rr]; a.cnt[r] = cnt ? cnt[rr] : nullptr;
     }
-    const size_t smem = (size_t)warps * nr * words * 4;
+    const size_t smem = (size_t)warps * ((size_t)nr * words + BG_LIST) * 4;
     // enough CTAs per cloud to fill the GPU, each warp looping over centres
     int per_cloud = div_up(M, warps);
     const int want = div_up(148 * 4, B);
