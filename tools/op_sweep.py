@@ -65,9 +65,15 @@ def main():
                     'alg_GBps': B * (12 * N + 4 * M) / ms / 1e6, 'hbm_peak_GBps': peak,
                     'streamed_equiv_GBps': B * (M - 1) * N * 16 / ms / 1e6}
             if have_ref:
+                import deepclr_b200
                 rms = timed(lambda: ref_cuda.furthest_point_sample(xyz, M), max(3, args.iters // 3), warm=1)
                 ridx = ref_cuda.furthest_point_sample(xyz, M)
-                line.update(ref_ms=rms, speedup=rms / ms, bit_exact=bool(torch.equal(idx, ridx)))
+                deepclr_b200.set_fps_tie_rule('reference')
+                idx_ref_rule = pu.furthest_point_sample(xyz, M)
+                deepclr_b200.set_fps_tie_rule('lowest_index')
+                # default rule = lowest index: differs from the reference kernel only in rounds with bit-equal maxima
+                line.update(ref_ms=rms, speedup=rms / ms, bit_exact_reference_tie_rule=bool(torch.equal(idx_ref_rule, ridx)),
+                            equal_under_lowest_index_rule=bool(torch.equal(idx, ridx)))
             print(json.dumps(line), flush=True)
         else:
             idx = pu.furthest_point_sample(xyz, M)
