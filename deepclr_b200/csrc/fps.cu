@@ -259,7 +259,7 @@ extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoin
                    B, N, npoint, pt_stride);
     if (B == 0 || npoint == 0) return DCLR_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (N > 2048 && N <= FPS_MAX_RESIDENT_N) {             // exact pruned variant (fps_bucket.cu)
+    if (N > 2048 && N <= 131072) {                         // exact pruned variants (fps_bucket.cu, fps_bucket_l2.cu)
         void *ws = nullptr;
         DCLR_CUDA(cudaMallocAsync(&ws, fps_bucket_workspace_bytes(B, N), st));
         int used = 0;

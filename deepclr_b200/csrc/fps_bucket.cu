@@ -327,7 +327,10 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_
     }
 }
 
-size_t fps_bucket_workspace_bytes(int B, int N) { return (size_t)B * N * sizeof(float4) + 256; }
+// records [B*N] float4 (+ running minima [B*N] fp32 for the L2-resident variant, N > 16384)
+size_t fps_bucket_workspace_bytes(int B, int N) {
+    return (size_t)B * N * (sizeof(float4) + (N > 16384 ? sizeof(float) : 0)) + 256;
+}
 
 template <int NW, int PP>
 static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
@@ -345,11 +348,16 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
                       cudaStream_t st, int *used) {
     *used = 0;
     const int tie_ref = fps_tie_rule() == 1;
-    if (N <= 2048 || N > 16384 || npoint < 2) return DCLR_OK;
+    if (N <= 2048 || N > 131072 || npoint < 2) return DCLR_OK;
     float4 *sorted = (float4 *)ws;
     fps_sort_kernel<<<B, FS_T, 0, st>>>(pts, stride, N, sorted);
     DCLR_LAUNCH_CHECK("fps_sort_kernel");
     int rc;
+    if (N > 16384) {                    // point state in L2 (fps_bucket_l2.cu); block of the reference kernel = 1024
+        rc = fps_bucket_l2_launch(sorted, (float *)(sorted + (size_t)B * N), B, N, npoint, tie_ref ? 10 : -1, idx, nx, st);
+        if (rc == DCLR_OK) *used = 1;
+        return rc;
+    }
     static const int shape = getenv("DCLR_FPS_SHAPE") ? atoi(getenv("DCLR_FPS_SHAPE")) : 0;   // tuning knob (tools/)
     if (N <= 4096) rc = launch_bucket<32, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     else if (N <= 8192) rc = launch_bucket<32, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);

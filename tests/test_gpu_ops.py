@@ -40,7 +40,7 @@ def test_golden_ops(p2):
 
 @pytest.mark.parametrize('B,N,npoint', [(1, 1, 1), (2, 33, 33), (3, 96, 1024), (2, 1000, 100), (2, 1024, 512),
                                         (1, 2500, 300), (2, 5000, 257), (1, 9000, 128), (2, 16384, 1024),
-                                        (1, 20000, 64)])
+                                        (1, 20000, 64), (2, 33333, 150), (1, 70001, 200), (1, 140000, 40)])
 def test_fps_matches_oracle(p2, B, N, npoint):
     rng = np.random.default_rng(N + npoint)
     xyz = rng.uniform(-40, 40, (B, N, 3)).astype(np.float32)

@@ -42,11 +42,13 @@ def reference_tie_rule():
 
 @pytest.mark.parametrize('kind,B,N,npoint', [('lattice', 2, 700, 300), ('lattice', 2, 3000, 600), ('dup', 3, 1024, 512),
                                              ('dup', 2, 5000, 700), ('dup', 2, 16384, 1024), ('dup', 1, 20000, 300),
-                                             ('kitti', 16, 16384, 1024), ('kitti', 2, 40000, 2500)])
+                                             ('kitti', 16, 16384, 1024), ('kitti', 2, 40000, 2500), ('dup', 1, 70001, 600),
+                                             ('lattice', 1, 100000, 300), ('kitti', 2, 131072, 1024)])
 def test_fps_reference_tie_rule_is_bit_identical_to_reference_kernel(p2, reference_tie_rule, kind, B, N, npoint):
     """With dclr_set_fps_tie_rule(1) the sampled indices equal the reference kernel's on EVERY input, exact ties
     included: integer lattices and duplicated points (many bit-equal maxima), and 16 full-size KITTI-shaped scans
-    (where ~1 round in 10^4 ties by chance).  All three kernels: resident (N <= 2048), bucketed, streaming."""
+    (where ~1 round in 10^4 ties by chance).  All kernels: resident (N <= 2048), bucketed in shared memory
+    (<= 16384), bucketed with the point state in L2 (<= 131072; one and two buckets per thread)."""
     from deepclr_b200 import synth
     rng = np.random.default_rng(N + npoint)
     if kind == 'lattice':
