@@ -30,6 +30,10 @@ _SIGNATURES = {
     'dclr_get_fps_tie_rule': (ctypes.c_int, []),
     'dclr_fps': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_gather': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    'dclr_pose_to_matrix': (c_int, [c_void_p, c_int, c_int, ctypes.c_float, c_void_p, c_void_p]),
+    'dclr_pose_errors': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    'dclr_gather_grad': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    'dclr_group_grad': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_ball_query': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
                                 c_int, c_void_p]),
     'dclr_group': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -30,6 +30,26 @@ __global__ void group_kernel(const float *__restrict__ feat, const int32_t *__re
     out[((size_t)b * C + c) * M * ns + e] = __ldg(feat + ((size_t)b * C + c) * N + __ldg(idx + (size_t)b * M * ns + e));
 }
 
+// backward of the two: scatter-add of the upstream gradient into the source positions.  Same arithmetic as the
+// reference's gather_points_grad_kernel_fast (sampling_gpu.cu:46-63) and group_points_grad_kernel_fast
+// (group_points_gpu.cu:8-25): fp32 atomicAdd per element, so equal to them up to the order of the additions.
+__global__ void gather_grad_kernel(const float *__restrict__ grad_out, const int32_t *__restrict__ idx, int C, int N,
+                                   int M, float *__restrict__ grad_points) {
+    int b = blockIdx.z, c = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= M) return;
+    atomicAdd(grad_points + ((size_t)b * C + c) * N + __ldg(idx + (size_t)b * M + j),
+              __ldg(grad_out + ((size_t)b * C + c) * M + j));
+}
+
+__global__ void group_grad_kernel(const float *__restrict__ grad_out, const int32_t *__restrict__ idx, int C, int N,
+                                  int M, int ns, float *__restrict__ grad_points) {
+    int b = blockIdx.z, c = blockIdx.y;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // over M*ns
+    if (e >= (size_t)M * ns) return;
+    atomicAdd(grad_points + ((size_t)b * C + c) * N + __ldg(idx + (size_t)b * M * ns + e),
+              __ldg(grad_out + ((size_t)b * C + c) * M * ns + e));
+}
+
 // ------------------------------------------------------------------ ball query
 constexpr int BQ_TILE = 2048;     // points per stage
 constexpr int BQ_WARPS = 8;
@@ -463,6 +483,31 @@ extern "C" int dclr_group(const float *feat, const int32_t *idx, int B, int C, i
     group_kernel<<<dim3((unsigned)((total + 255) / 256), C, B), 256, 0, (cudaStream_t)stream>>>(feat, idx, C, N, M,
                                                                                                 nsample, out);
     DCLR_LAUNCH_CHECK("group_kernel");
+    return DCLR_OK;
+}
+
+extern "C" int dclr_gather_grad(const float *grad_out, const int32_t *idx, int B, int C, int N, int M,
+                                float *grad_points, void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(grad_out && idx && grad_points, "dclr_gather_grad: null pointer");
+    DCLR_CHECK_ARG(B >= 0 && C >= 1 && N >= 1 && M >= 0 && C <= 65535 && B <= 65535, "dclr_gather_grad: bad shape");
+    if (B == 0 || M == 0) return DCLR_OK;
+    gather_grad_kernel<<<dim3(div_up(M, 256), C, B), 256, 0, (cudaStream_t)stream>>>(grad_out, idx, C, N, M, grad_points);
+    DCLR_LAUNCH_CHECK("gather_grad_kernel");
+    return DCLR_OK;
+}
+
+extern "C" int dclr_group_grad(const float *grad_out, const int32_t *idx, int B, int C, int N, int M, int nsample,
+                               float *grad_points, void *stream) {
+    using namespace dclr;
+    DCLR_CHECK_ARG(grad_out && idx && grad_points, "dclr_group_grad: null pointer");
+    DCLR_CHECK_ARG(B >= 0 && C >= 1 && N >= 1 && M >= 0 && nsample >= 0 && C <= 65535 && B <= 65535,
+                   "dclr_group_grad: bad shape");
+    if (B == 0 || M == 0 || nsample == 0) return DCLR_OK;
+    size_t total = (size_t)M * nsample;
+    group_grad_kernel<<<dim3((unsigned)((total + 255) / 256), C, B), 256, 0, (cudaStream_t)stream>>>(
+        grad_out, idx, C, N, M, nsample, grad_points);
+    DCLR_LAUNCH_CHECK("group_grad_kernel");
     return DCLR_OK;
 }
 

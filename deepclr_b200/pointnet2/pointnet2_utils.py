@@ -54,12 +54,13 @@ class GatherOperation(Function):
 
     @staticmethod
     def backward(ctx, grad_out):
-        # scatter-add of the reference's gather_points_grad kernel (sampling_gpu.cu:46-63), expressed in torch:
-        # training is outside the accelerated path
+        # scatter-add, as the reference's gather_points_grad kernel (pointnet2_utils.py:60-73, sampling_gpu.cu:46-63)
         idx, = ctx.saved_tensors
-        B, C, _ = grad_out.shape
-        grad = grad_out.new_zeros((B, C, ctx.n))
-        grad.scatter_add_(2, idx.long().unsqueeze(1).expand(-1, C, -1), grad_out.contiguous())
+        B, C, M = grad_out.shape
+        grad = torch.zeros((B, C, ctx.n), dtype=torch.float32, device=grad_out.device)
+        g = grad_out.contiguous().float()
+        with torch.cuda.device(grad_out.device):
+            _call('dclr_gather_grad', _lib.ptr(g), _lib.ptr(idx), B, C, ctx.n, M, _lib.ptr(grad))
         return grad, None
 
 
@@ -84,10 +85,13 @@ class GroupingOperation(Function):
 
     @staticmethod
     def backward(ctx, grad_out: torch.Tensor) -> Tuple[torch.Tensor, None]:
+        # scatter-add, as the reference's group_points_grad kernel (pointnet2_utils.py:181-197, group_points_gpu.cu:8-25)
         idx, = ctx.saved_tensors
         B, C, M, ns = grad_out.shape
-        grad = grad_out.new_zeros((B, C, ctx.n))
-        grad.scatter_add_(2, idx.long().view(B, 1, M * ns).expand(-1, C, -1), grad_out.contiguous().view(B, C, M * ns))
+        grad = torch.zeros((B, C, ctx.n), dtype=torch.float32, device=grad_out.device)
+        g = grad_out.contiguous().float()
+        with torch.cuda.device(grad_out.device):
+            _call('dclr_group_grad', _lib.ptr(g), _lib.ptr(idx), B, C, ctx.n, M, ns, _lib.ptr(grad))
         return grad, None
 
 

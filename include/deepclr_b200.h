@@ -75,6 +75,18 @@ int dclr_group(const float *feat, const int32_t *idx, int B, int C, int N, int M
                void *stream);
 
 /*
+ * Backward of gather / group: grad_points[b,c,idx[...]] += grad_out[...]  (fp32 atomicAdd; grad_points [B,C,N] must be
+ * zero-filled by the caller, as the reference's autograd Functions do: pointnet2_utils.py:65-70, 189-194).
+ * Replace pointnet2_cuda.gather_points_grad_wrapper (sampling.cpp:23-33 -> sampling_gpu.cu:46-72) and
+ * group_points_grad_wrapper (group_points.cpp:11-22 -> group_points_gpu.cu:8-44).  Equal to the reference up to the
+ * order of the floating-point additions (both sides use atomics).
+ */
+int dclr_gather_grad(const float *grad_out, const int32_t *idx, int B, int C, int N, int M, float *grad_points,
+                     void *stream);
+int dclr_group_grad(const float *grad_out, const int32_t *idx, int B, int C, int N, int M, int nsample,
+                    float *grad_points, void *stream);
+
+/*
  * Batched kNN.  Replaces torch_cluster.knn(x, y, k, batch_x, batch_y) as called at deepclr/models/deepclr.py:164-166
  * (equal-sized, sorted batches).  x [B*Nx,3] candidates, y [B*Ny,3] queries.  row_out/col_out [B*Ny*k] int64:
  * row = global y row id, col = global x row id, ascending distance, ties -> lower x index.  Needs 0 < k <= min(Nx,128).
@@ -151,6 +163,17 @@ int dclr_model_collect_timing(dclr_model *m, float *stage_ms_sum, int *calls_out
  * (source index local to the pair); 4 ball idx scale0 (compact, only the first cnt slots of a row are defined)
  * [2B,npoint,ns0] i32; 5 ball idx scale1. */
 int dclr_model_debug_copy(const dclr_model *m, int which, void *dst, size_t nbytes, void *stream);
+
+/* ------------------------------------------------------------------ post-processing on the device
+ * Pose labels -> 4x4 matrices, batched, float64: LabelType.to_matrix (deepclr/data/labels.py:80-101; dual quaternions
+ * are normalised by |real| + 1e-8 first, :46-51).  labels [B, 6|7|8] fp32 as the network emits them, label_type as in
+ * dclr_arch, scale = the label scale the reference divides by (<= 0: none).  T_out [B,16] row-major.
+ * Replaces the per-pair host loop of scripts/inference.py:113-119. */
+int dclr_pose_to_matrix(const float *labels, int B, int label_type, float scale, double *T_out, void *stream);
+/* KITTI odometry errors between two batches of 4x4 matrices (deepclr/evaluation/metrics.py:8-49): for each pair the
+ * smaller of err(m1 inv(m2)) and err(m2 inv(m1)); rotation in RADIANS (acos((trace-1)/2) clamped), translation = norm
+ * of the translation part. */
+int dclr_pose_errors(const double *T1, const double *T2, int B, double *rot_rad_out, double *trans_out, void *stream);
 
 #ifdef __cplusplus
 }

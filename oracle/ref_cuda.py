@@ -21,6 +21,8 @@ _SYMS = {
     'gather': '_Z34gather_points_kernel_launcher_fastiiiiPKfPKiPfP11CUstream_st',
     'ball': '_Z31ball_query_kernel_launcher_fastiiifiPKfS0_PiP11CUstream_st',
     'group': '_Z33group_points_kernel_launcher_fastiiiiiPKfPKiPfP11CUstream_st',
+    'gather_grad': '_Z39gather_points_grad_kernel_launcher_fastiiiiPKfPKiPfP11CUstream_st',
+    'group_grad': '_Z38group_points_grad_kernel_launcher_fastiiiiiPKfPKiPfP11CUstream_st',
 }
 
 
@@ -37,6 +39,8 @@ def lib():
         getattr(_lib, _SYMS['gather']).argtypes = [i, i, i, i, vp, vp, vp, vp]
         getattr(_lib, _SYMS['ball']).argtypes = [i, i, i, f, i, vp, vp, vp, vp]
         getattr(_lib, _SYMS['group']).argtypes = [i, i, i, i, i, vp, vp, vp, vp]
+        getattr(_lib, _SYMS['gather_grad']).argtypes = [i, i, i, i, vp, vp, vp, vp]
+        getattr(_lib, _SYMS['group_grad']).argtypes = [i, i, i, i, i, vp, vp, vp, vp]
         for s in _SYMS.values():
             getattr(_lib, s).restype = None
     return _lib
@@ -84,6 +88,22 @@ def grouping_operation(features: torch.Tensor, idx: torch.Tensor) -> torch.Tenso
     out = torch.empty((B, C, M, ns), dtype=torch.float32, device=features.device)
     getattr(lib(), _SYMS['group'])(B, C, N, M, ns, _p(features), _p(idx), _p(out), _st())
     return out
+
+
+def gather_operation_grad(grad_out: torch.Tensor, idx: torch.Tensor, N: int) -> torch.Tensor:
+    """pointnet2_utils.py:60-73: grad_features zero-filled by the caller, then gather_points_grad_wrapper."""
+    B, C, M = grad_out.shape
+    grad = torch.zeros((B, C, N), dtype=torch.float32, device=grad_out.device)
+    getattr(lib(), _SYMS['gather_grad'])(B, C, N, M, _p(grad_out.contiguous()), _p(idx), _p(grad), _st())
+    return grad
+
+
+def grouping_operation_grad(grad_out: torch.Tensor, idx: torch.Tensor, N: int) -> torch.Tensor:
+    """pointnet2_utils.py:181-197: group_points_grad_wrapper(B, C, N, npoint, nsample, grad_out, idx, grad_features)."""
+    B, C, M, ns = grad_out.shape
+    grad = torch.zeros((B, C, N), dtype=torch.float32, device=grad_out.device)
+    getattr(lib(), _SYMS['group_grad'])(B, C, N, M, ns, _p(grad_out.contiguous()), _p(idx), _p(grad), _st())
+    return grad
 
 
 def knn_standin(x: torch.Tensor, y: torch.Tensor, k: int, B: int) -> torch.Tensor:

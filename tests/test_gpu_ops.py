@@ -199,3 +199,44 @@ def test_full_size_properties(p2):
         row = bq[b, 5]
         uniq = row[:len(set(row.tolist()))]
         assert (np.diff(uniq) > 0).all()                                 # ascending index order
+
+
+@pytest.mark.parametrize('lt_name', ['POSE3D_EULER', 'POSE3D_QUAT', 'POSE3D_DUAL_QUAT'])
+def test_device_to_matrix_and_kitti_errors_match_host(lt_name):
+    """Batched on-device label -> matrix and KITTI errors (dclr_pose_to_matrix / dclr_pose_errors, float64) against the
+    host restatement of LabelType.to_matrix (deepclr/data/labels.py:80-101) and of the error definitions
+    (deepclr/evaluation/metrics.py:8-49).  Tolerance 1e-12: same float64 formulas."""
+    from deepclr_b200.data import device as dev_post
+    from deepclr_b200.data.labels import LabelType
+    lt = getattr(LabelType, lt_name)
+    rng = np.random.default_rng(11)
+    B = 200
+    mats = []
+    for _ in range(2 * B):
+        ang = rng.uniform(-0.3, 0.3, 3)
+        m = np.eye(4)
+        cx, sx, cy, sy, cz, sz = np.cos(ang[0]), np.sin(ang[0]), np.cos(ang[1]), np.sin(ang[1]), np.cos(ang[2]), np.sin(ang[2])
+        m[:3, :3] = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]) @ np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]]) \
+            @ np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+        m[:3, 3] = rng.uniform(-2, 2, 3)
+        mats.append(m)
+    labels = np.stack([lt.from_matrix(m) for m in mats]).astype(np.float32)
+    labels[:, :] *= rng.uniform(0.5, 2.0, (2 * B, 1)).astype(np.float32) if lt_name == 'POSE3D_DUAL_QUAT' else 1.0
+    want = np.stack([lt.to_matrix(l) for l in labels])
+    got = dev_post.to_matrix(_t(labels), lt)
+    np.testing.assert_allclose(got.cpu().numpy(), want, rtol=0, atol=1e-12)
+    got_s = dev_post.to_matrix(_t(labels * 3.0), lt, scale=3.0)
+    np.testing.assert_allclose(got_s.cpu().numpy(), np.stack([lt.to_matrix(l * 3.0, 3.0) for l in labels]), atol=1e-6)
+    rot, trans = dev_post.kitti_errors(got[:B], got[B:])
+
+    def host_err(a, b):
+        out = []
+        for p, q in ((a, b), (b, a)):
+            d = p @ np.linalg.inv(q)
+            out.append((np.arccos(max(min(0.5 * (d[0, 0] + d[1, 1] + d[2, 2] - 1.0), 1.0), -1.0)),
+                        np.linalg.norm(d[:3, 3])))
+        return min(out[0][0], out[1][0]), min(out[0][1], out[1][1])
+    ref = np.array([host_err(want[i], want[B + i]) for i in range(B)])
+    # acos amplifies rounding near 0 / pi; these rotations are well away from both
+    np.testing.assert_allclose(rot.cpu().numpy(), ref[:, 0], atol=1e-9)
+    np.testing.assert_allclose(trans.cpu().numpy(), ref[:, 1], atol=1e-12)

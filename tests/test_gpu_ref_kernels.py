@@ -102,3 +102,26 @@ def test_forward_close_to_reference_cuda_composition():
     for b in range(y.shape[0]):
         rot, trans = model_oracle.pose_errors(y[b], y_ref[b])
         assert rot <= 0.01 and trans <= 1e-3, (rot, trans)
+
+
+def test_gather_and_group_backward_equal_reference_kernels(p2):
+    """autograd through gather_operation / grouping_operation (dclr_gather_grad / dclr_group_grad) against the
+    reference's *_grad kernels on the same upstream gradient.  Both sides accumulate with fp32 atomicAdd, so they agree
+    up to the order of the additions: integer-valued gradients make every partial sum exact -> bit-equal."""
+    rng = np.random.default_rng(3)
+    B, C, N, M, ns = 2, 5, 700, 90, 24
+    feats = torch.from_numpy(rng.normal(size=(B, C, N)).astype(np.float32)).to(DEV).requires_grad_(True)
+    gidx = torch.from_numpy(rng.integers(0, N, (B, M)).astype(np.int32)).to(DEV)
+    qidx = torch.from_numpy(rng.integers(0, 60, (B, M, ns)).astype(np.int32)).to(DEV)     # many repeats per slot
+    up1 = torch.from_numpy(rng.integers(-8, 9, (B, C, M)).astype(np.float32)).to(DEV)
+    up2 = torch.from_numpy(rng.integers(-8, 9, (B, C, M, ns)).astype(np.float32)).to(DEV)
+    g1, = torch.autograd.grad(p2.gather_operation(feats, gidx), feats, up1)
+    g2, = torch.autograd.grad(p2.grouping_operation(feats, qidx), feats, up2)
+    assert torch.equal(g1, ref_cuda.gather_operation_grad(up1, gidx, N))
+    assert torch.equal(g2, ref_cuda.grouping_operation_grad(up2, qidx, N))
+    # real-valued gradients: equal to a float64 scatter-add within fp32 rounding
+    up3 = torch.from_numpy(rng.normal(size=(B, C, M, ns)).astype(np.float32)).to(DEV)
+    g3, = torch.autograd.grad(p2.grouping_operation(feats, qidx), feats, up3)
+    want = torch.zeros((B, C, N), dtype=torch.float64, device=DEV)
+    want.scatter_add_(2, qidx.long().view(B, 1, M * ns).expand(-1, C, -1), up3.double().view(B, C, M * ns))
+    torch.testing.assert_close(g3.double(), want, rtol=1e-5, atol=1e-5)
