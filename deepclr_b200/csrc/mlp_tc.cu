@@ -287,34 +287,34 @@ flow_tc_kernel(FlowArgs a) {
         __syncwarp();
         const uint32_t w1a = ptx::smem_u32(s_w1), w2a = ptx::smem_u32(s_w2), w3a = ptx::smem_u32(s_w3);
         uint32_t rphase[FLOW_SLOTS] = {0, 0};
+        // the whole warp runs the issue loop (converged); one elected lane issues each MMA / commit (ptx.cuh)
         for (int t0 = blockIdx.x * FLOW_SLOTS; t0 < a.num_tiles; t0 += tiles_per_iter) {
             for (int layer = 0; layer < 3; ++layer) {
                 for (int s = 0; s < FLOW_SLOTS; ++s) {
                     if (t0 + s >= a.num_tiles) continue;
-                    if (lane == 0) {
-                        ptx::mbar_wait(&ready[s], rphase[s] & 1);
-                        ptx::tc_fence_after();
-                        const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
-                        const uint32_t dcol = tmem_base + s * 256;
-                        if (layer == 0) {
-                            for (int ks = 0; ks < K0p / 16; ++ks)
-                                ptx::mma_f16_ss(dcol, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
-                                                make_sdesc(w1a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
-                        } else if (layer == 1) {
-                            for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
-                                ptx::mma_f16_ss(dcol + 128, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
-                                                make_sdesc(w2a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
-                        } else {
-                            for (int mb = 0; mb < H3 / 128; ++mb)
-                                for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
-                                    ptx::mma_f16_ss(dcol + mb * 128,
-                                                    make_sdesc(w3a + mb * (128 * 128 * 2) + ks * 2 * TC_LBO, TC_LBO),
-                                                    make_sdesc(act + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
-                        }
-                        ptx::mma_commit(&done[s]);
+                    ptx::mbar_wait(&ready[s], rphase[s] & 1);
+                    ptx::tc_fence_after();
+                    const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
+                    const uint32_t dcol = tmem_base + s * 256;
+                    if (layer == 0) {
+                        for (int ks = 0; ks < K0p / 16; ++ks)
+                            ptx::mma_f16_ss_warp(dcol, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
+                                                 make_sdesc(w1a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                    } else if (layer == 1) {
+#pragma unroll
+                        for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
+                            ptx::mma_f16_ss_warp(dcol + 128, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
+                                                 make_sdesc(w2a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                    } else {
+                        for (int mb = 0; mb < H3 / 128; ++mb)
+#pragma unroll
+                            for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
+                                ptx::mma_f16_ss_warp(dcol + mb * 128,
+                                                     make_sdesc(w3a + mb * (128 * 128 * 2) + ks * 2 * TC_LBO, TC_LBO),
+                                                     make_sdesc(act + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
                     }
+                    ptx::mma_commit_warp(&done[s]);
                     ++rphase[s];
-                    __syncwarp();
                 }
             }
         }
@@ -501,15 +501,15 @@ head_tc_kernel(HeadArgs a) {
             }
         }
     } else if (warp == HEAD_MMA_WARP) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer: the whole warp runs the loop, one elected lane issues ================
+        {
             const uint32_t act = ptx::smem_u32(s_act), wt = ptx::smem_u32(s_wt);
             uint32_t it = 0, n_ready = 0, fin_use[2] = {0, 0};
             for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
                     ptx::tc_fence_after();
-                    TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
+                    if (lane == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
                     const bool last = l == HEAD_LAYERS - 1;
                     for (int nc = 0; nc < a.out[l] / 128; ++nc) {
                         uint32_t dcol = tmem_base + nc * 128;
@@ -531,15 +531,15 @@ head_tc_kernel(HeadArgs a) {
                             for (int ks = 0; ks < kt / 16; ++ks) {
                                 const uint64_t xd = make_sdesc(act + ((k0 >> 3) + ks * 2) * TC_LBO, TC_LBO);
                                 const uint64_t wd = make_sdesc(wtile + ks * 2 * TC_LBO, TC_LBO);
-                                if (!last) ptx::mma_f16_ss(dcol, xd, wd, IDESC, (k0 | ks) > 0);
-                                else ptx::mma_f16_ss(dcol, wd, xd, IDESC, (k0 | ks) > 0);   // transposed
+                                if (!last) ptx::mma_f16_ss_warp(dcol, xd, wd, IDESC, (k0 | ks) > 0);
+                                else ptx::mma_f16_ss_warp(dcol, wd, xd, IDESC, (k0 | ks) > 0);   // transposed
                             }
-                            ptx::mma_commit(&empty[st]);               // frees the weight stage when the MMAs retire
+                            ptx::mma_commit_warp(&empty[st]);               // frees the weight stage when the MMAs retire
                         }
-                        if (last) ptx::mma_commit(&fin_done[nc & 1]);
+                        if (last) ptx::mma_commit_warp(&fin_done[nc & 1]);
                     }
-                    if (!last) ptx::mma_commit(layer_done);
-                    TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
+                    if (!last) ptx::mma_commit_warp(layer_done);
+                    if (lane == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
                 }
             }
         }
