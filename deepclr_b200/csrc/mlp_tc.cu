@@ -48,6 +48,15 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t smem_addr, uint32_t lbo_
            ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
 }
 
+// Descriptors in the issue loops: constant high word, low word advanced by an ADD per K step (the issuing warp's
+// integer work per MMA is serial latency in front of the tensor pipe).
+constexpr uint32_t SDESC_HI = (128u >> 4) | (1u << 14);                 // SBO = 128 B, version 1 (bits 32..47)
+constexpr uint32_t SDESC_KSTEP = (2u * TC_LBO) >> 4;                    // two 16-byte chunk columns = 16 K elements
+__device__ __forceinline__ uint32_t sdesc_lo(uint32_t smem_addr) {     // start address | LBO = TC_LBO
+    return ((smem_addr >> 4) & 0x3fffu) | ((uint32_t)(TC_LBO >> 4) << 16);
+}
+__device__ __forceinline__ uint64_t sdesc(uint32_t lo) { return ((uint64_t)SDESC_HI << 32) | lo; }
+
 template <typename T16> struct Cvt;
 template <> struct Cvt<__nv_bfloat16> {
     static constexpr int is_bf16 = 1;
@@ -285,7 +294,11 @@ flow_tc_kernel(FlowArgs a) {
             ptx::mbar_wait(wbar, 0);
         }
         __syncwarp();
-        const uint32_t w1a = ptx::smem_u32(s_w1), w2a = ptx::smem_u32(s_w2), w3a = ptx::smem_u32(s_w3);
+        const uint32_t w1_lo = sdesc_lo(ptx::smem_u32(s_w1)), w2_lo = sdesc_lo(ptx::smem_u32(s_w2)),
+                       w3_lo = sdesc_lo(ptx::smem_u32(s_w3));
+        uint32_t act_lo[FLOW_SLOTS];
+#pragma unroll
+        for (int s = 0; s < FLOW_SLOTS; ++s) act_lo[s] = sdesc_lo(ptx::smem_u32(s_act + s * act_bytes));
         uint32_t rphase[FLOW_SLOTS] = {0, 0};
         // the whole warp runs the issue loop (converged); one elected lane issues each MMA / commit (ptx.cuh)
         for (int t0 = blockIdx.x * FLOW_SLOTS; t0 < a.num_tiles; t0 += tiles_per_iter) {
@@ -294,24 +307,25 @@ flow_tc_kernel(FlowArgs a) {
                     if (t0 + s >= a.num_tiles) continue;
                     ptx::mbar_wait(&ready[s], rphase[s] & 1);
                     ptx::tc_fence_after();
-                    const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
                     const uint32_t dcol = tmem_base + s * 256;
+                    const uint32_t a_lo = act_lo[s];
                     if (layer == 0) {
                         for (int ks = 0; ks < K0p / 16; ++ks)
-                            ptx::mma_f16_ss_warp(dcol, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
-                                                 make_sdesc(w1a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                            ptx::mma_f16_ss_warp(dcol, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w1_lo + ks * SDESC_KSTEP), IDESC,
+                                                 ks > 0);
                     } else if (layer == 1) {
 #pragma unroll
                         for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
-                            ptx::mma_f16_ss_warp(dcol + 128, make_sdesc(act + ks * 2 * TC_LBO, TC_LBO),
-                                                 make_sdesc(w2a + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                            ptx::mma_f16_ss_warp(dcol + 128, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w2_lo + ks * SDESC_KSTEP),
+                                                 IDESC, ks > 0);
                     } else {
-                        for (int mb = 0; mb < H3 / 128; ++mb)
+                        for (int mb = 0; mb < H3 / 128; ++mb) {
+                            const uint32_t w_lo = w3_lo + mb * ((128u * 128 * 2) >> 4);
 #pragma unroll
                             for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
-                                ptx::mma_f16_ss_warp(dcol + mb * 128,
-                                                     make_sdesc(w3a + mb * (128 * 128 * 2) + ks * 2 * TC_LBO, TC_LBO),
-                                                     make_sdesc(act + ks * 2 * TC_LBO, TC_LBO), IDESC, ks > 0);
+                                ptx::mma_f16_ss_warp(dcol + mb * 128, sdesc(w_lo + ks * SDESC_KSTEP),
+                                                     sdesc(a_lo + ks * SDESC_KSTEP), IDESC, ks > 0);
+                        }
                     }
                     ptx::mma_commit_warp(&done[s]);
                     ++rphase[s];
@@ -503,15 +517,16 @@ head_tc_kernel(HeadArgs a) {
     } else if (warp == HEAD_MMA_WARP) {
         // ===================== MMA issuer: the whole warp runs the loop, one elected lane issues ================
         {
-            const uint32_t act = ptx::smem_u32(s_act), wt = ptx::smem_u32(s_wt);
-            uint32_t it = 0, n_ready = 0, fin_use[2] = {0, 0};
+            const uint32_t act_lo = sdesc_lo(ptx::smem_u32(s_act)), wt_lo = sdesc_lo(ptx::smem_u32(s_wt));
+            uint32_t st = 0, ph = 0, n_ready = 0, fin_use[2] = {0, 0};
             for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
                     ptx::tc_fence_after();
                     if (lane == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
                     const bool last = l == HEAD_LAYERS - 1;
-                    for (int nc = 0; nc < a.out[l] / 128; ++nc) {
+                    const int Kp = a.Kp[l], nblocks = a.out[l] / 128;
+                    for (int nc = 0; nc < nblocks; ++nc) {
                         uint32_t dcol = tmem_base + nc * 128;
                         if (last) {
                             const int buf = nc & 1;
@@ -522,19 +537,26 @@ head_tc_kernel(HeadArgs a) {
                             ++fin_use[buf];
                             dcol = tmem_base + buf * 128;
                         }
-                        for (int k0 = 0; k0 < a.Kp[l]; k0 += HEAD_KT, ++it) {
-                            const int st = it % HEAD_STAGES;
-                            ptx::mbar_wait(&full[st], (it / HEAD_STAGES) & 1);
+                        uint32_t a_lo = act_lo, acc = 0;
+                        for (int k0 = 0; k0 < Kp; k0 += HEAD_KT) {
+                            ptx::mbar_wait(&full[st], ph);
                             ptx::tc_fence_after();
-                            const int kt = min(HEAD_KT, a.Kp[l] - k0);
-                            const uint32_t wtile = wt + st * HEAD_TILE_BYTES;
-                            for (int ks = 0; ks < kt / 16; ++ks) {
-                                const uint64_t xd = make_sdesc(act + ((k0 >> 3) + ks * 2) * TC_LBO, TC_LBO);
-                                const uint64_t wd = make_sdesc(wtile + ks * 2 * TC_LBO, TC_LBO);
-                                if (!last) ptx::mma_f16_ss_warp(dcol, xd, wd, IDESC, (k0 | ks) > 0);
-                                else ptx::mma_f16_ss_warp(dcol, wd, xd, IDESC, (k0 | ks) > 0);   // transposed
+                            const uint32_t w_lo = wt_lo + st * (HEAD_TILE_BYTES >> 4);
+                            // hidden layers: D = X.W^T (A = activations); last layer transposed (A = weights)
+                            const uint32_t p_lo = last ? w_lo : a_lo, q_lo = last ? a_lo : w_lo;
+                            if (Kp - k0 >= HEAD_KT) {                       // full 64-wide K tile: 4 MMAs, no loop
+                                ptx::mma_f16_ss_warp(dcol, sdesc(p_lo), sdesc(q_lo), IDESC, acc);
+#pragma unroll
+                                for (int ks = 1; ks < HEAD_KT / 16; ++ks)
+                                    ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, 1u);
+                            } else {
+                                for (int ks = 0; ks < (Kp - k0) / 16; ++ks)
+                                    ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, ks ? 1u : acc);
                             }
-                            ptx::mma_commit_warp(&empty[st]);               // frees the weight stage when the MMAs retire
+                            acc = 1;
+                            a_lo += (HEAD_KT / 16) * SDESC_KSTEP;
+                            ptx::mma_commit_warp(&empty[st]);          // frees the weight stage when the MMAs retire
+                            if (++st == HEAD_STAGES) { st = 0; ph ^= 1; }
                         }
                         if (last) ptx::mma_commit_warp(&fin_done[nc & 1]);
                     }
