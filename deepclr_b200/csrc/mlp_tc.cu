@@ -447,8 +447,15 @@ flow_tc_kernel(FlowArgs a) {
 
 // ---------------------------------------------------------------- output head
 constexpr int HEAD_LAYERS = 5;
-constexpr int HEAD_KT = 64;                      // K elements per streamed weight tile (128 rows x 64 = 16 KB)
-constexpr int HEAD_STAGES = 5;
+// Weight ring shape (overridable for tools/ab.sh).  Every tile costs an exposed mbarrier wait + commit (~115 cycles,
+// tools/micro/mma_ring.cu), so tiles are as wide as the shared-memory budget allows: measured head time per 64 pairs
+// 64 x 5 stages 0.184 ms | 80 x 4 0.174 | 96 x 3 0.168 | 96 x 2 0.192 | 128 x 2 0.177 | **112 x 3 0.163**.
+#ifndef DCLR_HEAD_KT
+#define DCLR_HEAD_KT 112
+#define DCLR_HEAD_STAGES 3
+#endif
+constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 112 = 28 KB)
+constexpr int HEAD_STAGES = DCLR_HEAD_STAGES;
 constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
 constexpr int HEAD_EPI_WARPS = 8;                // 4 TMEM lane quarters x 2 column halves
 constexpr int HEAD_PROD_WARP = HEAD_EPI_WARPS, HEAD_MMA_WARP = HEAD_EPI_WARPS + 1;
@@ -544,7 +551,7 @@ head_tc_kernel(HeadArgs a) {
                             const uint32_t w_lo = wt_lo + st * (HEAD_TILE_BYTES >> 4);
                             // hidden layers: D = X.W^T (A = activations); last layer transposed (A = weights)
                             const uint32_t p_lo = last ? w_lo : a_lo, q_lo = last ? a_lo : w_lo;
-                            if (Kp - k0 >= HEAD_KT) {                       // full 64-wide K tile: 4 MMAs, no loop
+                            if (Kp - k0 >= HEAD_KT) {                       // full K tile: HEAD_KT / 16 MMAs, unrolled
                                 ptx::mma_f16_ss_warp(dcol, sdesc(p_lo), sdesc(q_lo), IDESC, acc);
 #pragma unroll
                                 for (int ks = 1; ks < HEAD_KT / 16; ++ks)
