@@ -183,15 +183,54 @@ template <int KC, typename T16>
 __device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&mk)[4], int k_rt, int g, int nvalid,
                                                float bias, uint16_t *__restrict__ out, float *__restrict__ out32,
                                                int ld) {
-    const int k = KC ? KC : k_rt;
+    if constexpr (KC > 0) {
+        // k known at compile time: column -> group is a constant, so the group maxima are G independent register
+        // chains (no counters, no branches); the stores follow as one short predicated sequence
+        constexpr int G = 128 / KC;
+        float gm[G];
+#pragma unroll
+        for (int q = 0; q < G; ++q) gm[q] = -INFINITY;
+        const bool any_masked = (mk[0] | mk[1] | mk[2] | mk[3]) != 0u;   // same for every thread of the slot
+#pragma unroll
+        for (int c0 = 0; c0 < 128; c0 += 64) {
+            uint32_t v0[32], v1[32];
+            ptx::tmem_ld32(taddr + c0, v0);
+            ptx::tmem_ld32(taddr + c0 + 32, v1);
+            ptx::tmem_ld_wait();
+            if (!any_masked) {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) {
+                    const int col = c0 + i;
+                    if (col / KC < G) gm[col / KC] = fmaxf(gm[col / KC], __uint_as_float(i < 32 ? v0[i & 31] : v1[i & 31]));
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) {
+                    const int col = c0 + i;
+                    const bool m = (mk[col >> 5] >> (col & 31)) & 1u;
+                    const float x = m ? -INFINITY : __uint_as_float(i < 32 ? v0[i & 31] : v1[i & 31]);
+                    if (col / KC < G) gm[col / KC] = fmaxf(gm[col / KC], x);
+                }
+            }
+        }
+        const int ng = min(min(g, nvalid), G);
+#pragma unroll
+        for (int q = 0; q < G; ++q) {
+            if (q < ng) {
+                const float val = fmaxf(gm[q] + bias, 0.f);
+                out[(size_t)q * ld] = Cvt<T16>::one(val);
+                if (out32) out32[(size_t)q * ld] = val;
+            }
+        }
+        return;
+    }
+    const int k = k_rt;
     float cur = -INFINITY;
     int cnt = 0, og = 0;
-    auto scan = [&](const uint32_t (&v)[32], uint32_t mword, auto masked_c) {
-        constexpr bool MASKED = decltype(masked_c)::value;
+    auto scan = [&](const uint32_t (&v)[32], uint32_t mword) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-            float x = __uint_as_float(v[i]);
-            if (MASKED && ((mword >> i) & 1u)) x = -INFINITY;
+            const float x = ((mword >> i) & 1u) ? -INFINITY : __uint_as_float(v[i]);
             cur = fmaxf(cur, x);
             if (++cnt == k) {
                 if (og < g && og < nvalid) {
@@ -203,21 +242,12 @@ __device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&
             }
         }
     };
-    // mword comes from shared memory and is the same for every thread of the slot: a uniform branch.  The radius mask is
-    // almost always empty (k nearest samples vs a 10 m merge radius), so the common path is a bare running max.
-    auto consume = [&](const uint32_t (&v)[32], uint32_t mword) {
-        if (mword == 0) scan(v, 0u, std::false_type{});
-        else scan(v, mword, std::true_type{});
-    };
-    // two TMEM loads in flight per wait
-#pragma unroll
-    for (int c0 = 0; c0 < 128; c0 += 64) {
-        uint32_t v0[32], v1[32];
-        ptx::tmem_ld32(taddr + c0, v0);
-        ptx::tmem_ld32(taddr + c0 + 32, v1);
+#pragma unroll 1
+    for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        ptx::tmem_ld32(taddr + c0, v);
         ptx::tmem_ld_wait();
-        consume(v0, mk[c0 >> 5]);
-        consume(v1, mk[(c0 >> 5) + 1]);
+        scan(v, mk[c0 >> 5]);
     }
 }
 
