@@ -28,8 +28,10 @@ size_t ball_grid_workspace_bytes(int B, int N);
 int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
                      const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad, void *ws,
                      cudaStream_t st, int *used);
+// nbr4 (optional) [B,Ny,k]: {x_cand - y_query (3 floats, the subtraction of the distance), candidate index bits} --
+// what the tensor-core flow kernel needs per row, in one aligned 16-byte record
 int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
-               int32_t *col_local, cudaStream_t st);
+               int32_t *col_local, float4 *nbr4, cudaStream_t st);
 
 // sa_mlp.cu
 struct SaArgs {

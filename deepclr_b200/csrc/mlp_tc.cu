@@ -97,6 +97,9 @@ template <> struct Cvt<__half> {
     static __device__ __forceinline__ float back(uint16_t h) { return __half2float(*reinterpret_cast<__half *>(&h)); }
 };
 
+__device__ __forceinline__ void ld_shared_v4(uint32_t addr, uint32_t &a, uint32_t &b, uint32_t &c, uint32_t &d) {
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -176,6 +179,10 @@ __device__ __forceinline__ void store_ones_chunks(uint32_t act_row_addr, int wid
     st_shared_v4(act_row_addr + (uint32_t)((width >> 3) + 1) * TC_LBO, 0u, 0u, 0u, 0u);
 }
 
+#ifndef DCLR_FLOW_EPI3_COLS
+#define DCLR_FLOW_EPI3_COLS 64
+#endif
+constexpr int FLOW_EPI3_COLS = DCLR_FLOW_EPI3_COLS;   // TMEM columns in flight per wait in the last flow epilogue (64 | 32)
 // Last flow layer (transposed): this thread's TMEM lane is one output channel, the 128 columns are the tile rows
 // (groups of k neighbours).  Radius-masked max per group, + bias, ReLU, store.  KC > 0: k known at compile time, the
 // group bookkeeping folds away and the per-group maxima become independent chains.
@@ -192,20 +199,20 @@ __device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&
         for (int q = 0; q < G; ++q) gm[q] = -INFINITY;
         const bool any_masked = (mk[0] | mk[1] | mk[2] | mk[3]) != 0u;   // same for every thread of the slot
 #pragma unroll
-        for (int c0 = 0; c0 < 128; c0 += 64) {
+        for (int c0 = 0; c0 < 128; c0 += FLOW_EPI3_COLS) {
             uint32_t v0[32], v1[32];
             ptx::tmem_ld32(taddr + c0, v0);
-            ptx::tmem_ld32(taddr + c0 + 32, v1);
+            if constexpr (FLOW_EPI3_COLS == 64) ptx::tmem_ld32(taddr + c0 + 32, v1);
             ptx::tmem_ld_wait();
             if (!any_masked) {
 #pragma unroll
-                for (int i = 0; i < 64; ++i) {
+                for (int i = 0; i < FLOW_EPI3_COLS; ++i) {
                     const int col = c0 + i;
                     if (col / KC < G) gm[col / KC] = fmaxf(gm[col / KC], __uint_as_float(i < 32 ? v0[i & 31] : v1[i & 31]));
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 64; ++i) {
+                for (int i = 0; i < FLOW_EPI3_COLS; ++i) {
                     const int col = c0 + i;
                     const bool m = (mk[col >> 5] >> (col & 31)) & 1u;
                     const float x = m ? -INFINITY : __uint_as_float(i < 32 ? v0[i & 31] : v1[i & 31]);
@@ -256,16 +263,16 @@ __device__ __forceinline__ void flow_group_max(uint32_t taddr, const uint32_t (&
 // tools/head_trace.py: SM-clock timestamps of CTA 0's roles (build -DDCLR_TRACE only)
 __device__ long long g_trace[1024];
 __device__ long long g_flow_trace[1024];
-#define FLTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && q == 0 && half == 0 && s == 0 && ft < 8) g_flow_trace[ft * 16 + (slot)] = clock64(); } while (0)
+#define FLTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && q == 0 && half == 0 && s == 0 && ft >= 0 && ft < 8) g_flow_trace[ft * 16 + (slot)] = clock64(); } while (0)
 #define TRACE(slot) do { if (blockIdx.x == 0 && (slot) < 1024) g_trace[(slot)] = clock64(); } while (0)
 #else
 #define FLTRACE(slot) do { } while (0)
 #define TRACE(slot) do { } while (0)
 #endif
 struct FlowArgs {
-    const float *xyz;       // [2B, n, 3] sampled coordinates, templates first
-    const uint16_t *feat;   // [2B, n, F] point-major set-abstraction features, 16-bit operand format
-    const int32_t *nbr;     // [B, n, k] source index (local to the pair) of the k nearest source samples
+    const uint16_t *feat;   // [2B, n, F] point-major set-abstraction features, 16-bit operand format, templates first
+    const float4 *nbr;      // [B, n, k] per row: {source - template displacement, source index (local to the pair)} of
+                            // the k nearest source samples, written by the kNN kernel (pointops.cu)
     const uint16_t *w;      // packed images: W1 [128 x K0p] | W2 [128 x 128] | W3 [H3 x 128] (128-row blocks)
     const float *bias;      // b1[128] b2[128] b3[H3]
     uint16_t *out;          // [B*n, H3] motion features, 16-bit (coordinates are kept in xyz)
@@ -279,7 +286,16 @@ constexpr int FLOW_SLOTS = 2;
 constexpr int FLOW_K2P = 128 + 16;     // layer-2 K: 128 hidden + [b_hi, b_lo, 0 ...] against the ones chunks
 constexpr int FLOW_WPS = 8;           // build/epilogue warps per slot: 4 TMEM lane quarters x 2 column halves
 constexpr int FLOW_MMA_WARP = FLOW_SLOTS * FLOW_WPS;
-constexpr int FLOW_THREADS = (FLOW_MMA_WARP + 1) * 32;
+#ifndef DCLR_FLOW_STAGE
+#define DCLR_FLOW_STAGE 0
+#endif
+#ifndef DCLR_FLOW_PROD
+#define DCLR_FLOW_PROD 1
+#endif
+constexpr int FLOW_STAGE_BYTES = DCLR_FLOW_STAGE;   // per gather warp: staging area for a tile's distinct template rows
+constexpr int FLOW_PROD = DCLR_FLOW_PROD;           // gather (cp.async) warps per slot; 19 warps = at most 5 per SM
+                                                    // sub-partition = 96 registers per thread
+constexpr int FLOW_THREADS = (FLOW_MMA_WARP + 1 + FLOW_SLOTS * FLOW_PROD) * 32;
 
 template <typename T16>
 __global__ void __launch_bounds__(FLOW_THREADS, 1)
@@ -292,16 +308,22 @@ flow_tc_kernel(FlowArgs a) {
     uint8_t *s_w1 = smem, *s_w2 = s_w1 + w1_bytes, *s_w3 = s_w2 + w2_bytes;
     uint8_t *s_act = s_w3 + w3_bytes;                                    // FLOW_SLOTS x act_bytes
     float *s_bias = reinterpret_cast<float *>(s_act + FLOW_SLOTS * act_bytes);   // 256 + H3 floats
-    uint32_t *s_maskw = reinterpret_cast<uint32_t *>(s_bias + 256 + H3);         // [FLOW_SLOTS][4]
-    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_maskw + FLOW_SLOTS * 4);    // wbar, ready[2], done[2]
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 1 + 2 * FLOW_SLOTS);
-    uint64_t *wbar = s_bar, *ready = s_bar + 1, *done = s_bar + 1 + FLOW_SLOTS;
+    float4 *s_nbr = reinterpret_cast<float4 *>(s_bias + 256 + H3);               // [FLOW_SLOTS][128] row records
+    uint8_t *s_stage = reinterpret_cast<uint8_t *>(s_nbr + FLOW_SLOTS * 128);    // per gather warp: template rows of a tile
+    uint32_t *s_maskw = reinterpret_cast<uint32_t *>(s_stage + FLOW_SLOTS * FLOW_PROD * FLOW_STAGE_BYTES);   // [2 parities][FLOW_SLOTS][4]
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_maskw + 2 * FLOW_SLOTS * 4);    // wbar, ready, done, idx, free, gath
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 1 + 5 * FLOW_SLOTS);
+    uint64_t *wbar = s_bar, *ready = s_bar + 1, *done = s_bar + 1 + FLOW_SLOTS, *idx_ready = s_bar + 1 + 2 * FLOW_SLOTS;
+    uint64_t *act_free = s_bar + 1 + 3 * FLOW_SLOTS, *gath = s_bar + 1 + 4 * FLOW_SLOTS;
 
     if (tid == 0) {
         ptx::mbar_init(wbar, 1);
         for (int s = 0; s < FLOW_SLOTS; ++s) {
             ptx::mbar_init(&ready[s], FLOW_WPS * 32);
             ptx::mbar_init(&done[s], 1);
+            ptx::mbar_init(&idx_ready[s], 32);
+            ptx::mbar_init(&act_free[s], 1);
+            ptx::mbar_init(&gath[s], FLOW_PROD * 32);
         }
         ptx::fence_mbar_init();
     }
@@ -316,6 +338,26 @@ flow_tc_kernel(FlowArgs a) {
 
     if (warp == FLOW_MMA_WARP) {
         // ===================== weight load (once) + MMA issue =====================
+        // The row records of a slot's NEXT tile ({displacement, source index}, 16 bytes per row) travel global -> shared
+        // by cp.async from this (mostly idle) warp: no other warp of the kernel loads coordinates or indices from
+        // global memory.  The 128 records of a tile are contiguous: nbr[(b n + p0) k + r], r < g k.  Always one
+        // arrival per lane, copy or not.
+        auto prefetch_idx = [&](const int tile, const int s) {
+            if (tile < a.num_tiles) {
+                const int b = tile / a.tiles_per_pair;
+                const int p0 = (tile - b * a.tiles_per_pair) * a.groups_per_tile;
+                const int rows = min(a.groups_per_tile, a.n - p0) * a.k;
+                const float4 *src = a.nbr + ((size_t)b * a.n + p0) * a.k;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = i * 32 + lane;
+                    if (r < rows) ptx::cp_async16_cg(ptx::smem_u32(s_nbr + s * 128 + r), src + r, 16);
+                }
+            }
+            ptx::cp_async_mbar_arrive_noinc(&idx_ready[s]);
+        };
+#pragma unroll
+        for (int s = 0; s < FLOW_SLOTS; ++s) prefetch_idx(blockIdx.x * FLOW_SLOTS + s, s);
         if (lane == 0) {
             ptx::mbar_expect_tx(wbar, w1_bytes + w2_bytes + w3_bytes);
             ptx::bulk_g2s(s_w1, a.w, w1_bytes, wbar);
@@ -329,43 +371,188 @@ flow_tc_kernel(FlowArgs a) {
         uint32_t act_lo[FLOW_SLOTS];
 #pragma unroll
         for (int s = 0; s < FLOW_SLOTS; ++s) act_lo[s] = sdesc_lo(ptx::smem_u32(s_act + s * act_bytes));
-        uint32_t rphase[FLOW_SLOTS] = {0, 0};
-        // the whole warp runs the issue loop (converged); one elected lane issues each MMA / commit (ptx.cuh)
-        for (int t0 = blockIdx.x * FLOW_SLOTS; t0 < a.num_tiles; t0 += tiles_per_iter) {
-            for (int layer = 0; layer < 3; ++layer) {
-                for (int s = 0; s < FLOW_SLOTS; ++s) {
-                    if (t0 + s >= a.num_tiles) continue;
-                    ptx::mbar_wait(&ready[s], rphase[s] & 1);
-                    ptx::tc_fence_after();
-                    const uint32_t dcol = tmem_base + s * 256;
-                    const uint32_t a_lo = act_lo[s];
-                    if (layer == 0) {
-                        for (int ks = 0; ks < K0p / 16; ++ks)
-                            ptx::mma_f16_ss_warp(dcol, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w1_lo + ks * SDESC_KSTEP), IDESC,
-                                                 ks > 0);
-                    } else if (layer == 1) {
+        // The whole warp runs the issue loop (converged); one elected lane issues each MMA / commit (ptx.cuh).
+        // Slots are served in the order they become ready, not round-robin: a fixed s0, s1, s0, ... order locks the two
+        // slots into the same phase (each waited ~1150 extra cycles per layer for the other's MMAs, both gathered and
+        // both reduced at the same time, tensor pipe idle meanwhile); served on demand they drift into anti-phase.
+        uint32_t rphase[FLOW_SLOTS], layer[FLOW_SLOTS];
+        int tile[FLOW_SLOTS];
+        bool live[FLOW_SLOTS];
+        bool any_live = false;
 #pragma unroll
-                        for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
-                            ptx::mma_f16_ss_warp(dcol + 128, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w2_lo + ks * SDESC_KSTEP),
-                                                 IDESC, ks > 0);
-                    } else {
-                        for (int mb = 0; mb < H3 / 128; ++mb) {
-                            const uint32_t w_lo = w3_lo + mb * ((128u * 128 * 2) >> 4);
+        for (int s = 0; s < FLOW_SLOTS; ++s) {
+            rphase[s] = 0; layer[s] = 0;
+            tile[s] = blockIdx.x * FLOW_SLOTS + s;
+            live[s] = tile[s] < a.num_tiles;
+            any_live |= live[s];
+        }
+        while (any_live) {
 #pragma unroll
-                            for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
-                                ptx::mma_f16_ss_warp(dcol + mb * 128, sdesc(w_lo + ks * SDESC_KSTEP),
-                                                     sdesc(a_lo + ks * SDESC_KSTEP), IDESC, ks > 0);
-                        }
+            for (int s = 0; s < FLOW_SLOTS; ++s) {
+                if (!live[s]) continue;
+                if (!__all_sync(0xffffffffu, ptx::mbar_try_wait(&ready[s], rphase[s] & 1))) continue;   // warp-uniform
+                ptx::tc_fence_after();
+                const uint32_t dcol = tmem_base + s * 256;
+                const uint32_t a_lo = act_lo[s];
+                if (layer[s] == 0) {
+                    for (int ks = 0; ks < K0p / 16; ++ks)
+                        ptx::mma_f16_ss_warp(dcol, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w1_lo + ks * SDESC_KSTEP), IDESC,
+                                             ks > 0);
+                } else if (layer[s] == 1) {
+#pragma unroll
+                    for (int ks = 0; ks < FLOW_K2P / 16; ++ks)
+                        ptx::mma_f16_ss_warp(dcol + 128, sdesc(a_lo + ks * SDESC_KSTEP), sdesc(w2_lo + ks * SDESC_KSTEP),
+                                             IDESC, ks > 0);
+                } else {
+                    for (int mb = 0; mb < H3 / 128; ++mb) {
+                        const uint32_t w_lo = w3_lo + mb * ((128u * 128 * 2) >> 4);
+#pragma unroll
+                        for (int ks = 0; ks < 8; ++ks)      // transposed: A = weights, B = activations
+                            ptx::mma_f16_ss_warp(dcol + mb * 128, sdesc(w_lo + ks * SDESC_KSTEP),
+                                                 sdesc(a_lo + ks * SDESC_KSTEP), IDESC, ks > 0);
                     }
-                    ptx::mma_commit_warp(&done[s]);
-                    ++rphase[s];
+                }
+                ptx::mma_commit_warp(&done[s]);
+                ++rphase[s];
+                if (layer[s] == 0) {
+                    // every thread of slot s has read its index (they arrived on ready[s]): refill for the next tile
+                    prefetch_idx(tile[s] + tiles_per_iter, s);
+                    layer[s] = 1;
+                } else if (layer[s] == 1) {
+                    layer[s] = 2;
+                } else {
+                    ptx::mma_commit_warp(&act_free[s]);                // operand buffer free: the gather warp goes on
+                    layer[s] = 0;
+                    tile[s] += tiles_per_iter;
+                    live[s] = tile[s] < a.num_tiles;
                 }
             }
+            any_live = false;
+#pragma unroll
+            for (int s = 0; s < FLOW_SLOTS; ++s) any_live |= live[s];
+        }
+    } else if (warp > FLOW_MMA_WARP) {
+        // ===================== feature gather (FLOW_PROD cp.async warps per slot) =====================
+        // Row r of a tile = (point p0 + r / k, neighbour r % k) = [f_tmpl | f_src | dp hi,hi,lo | 0].  The two 128-byte
+        // feature blocks of every row go global -> shared by 16-byte cp.async as soon as the slot's operand buffer is
+        // free (the previous tile's last MMA has completed), i.e. while the epilogue warps still reduce that tile.
+        // Random 128-byte rows of the L2-resident feature table arrive at ~15 B/cycle/SM whatever the lane mapping,
+        // instruction or depth (tools/micro/lsu_gather.cu; TMA tile::gather4 manages 7, tools/micro/gather4.cu), so a
+        // tile's 32 KB need ~2k cycles and the issuing warp is blocked for most of them: that is why the gather has
+        // warp of its own.  One instruction covers 8 rows x 4 chunks: 8 lines for L1tex, and the 8 lanes of a
+        // shared-memory store phase hit 8 different rows = all 32 banks.  Rows that do not exist are zero-filled.
+        const int pw = warp - FLOW_MMA_WARP - 1, s = pw / FLOW_PROD, part = pw % FLOW_PROD;
+        constexpr int RG = 128 / 8 / FLOW_PROD;                        // 8-row groups per gather warp
+        const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
+        const uint32_t stage = ptx::smem_u32(s_stage + pw * FLOW_STAGE_BYTES);    // one staging area per gather warp
+        const int k = a.k, n = a.n, F = a.F, g = a.groups_per_tile, fc = F / 8, cq = lane >> 3;
+        int prow[RG], pgrp[RG];
+#pragma unroll
+        for (int i = 0; i < RG; ++i) { prow[i] = part * (128 / FLOW_PROD) + i * 8 + (lane & 7); pgrp[i] = prow[i] / k; }
+        // FC = chunks per feature block when known at compile time (0: runtime fc).  This warp is bound by its own
+        // instruction issue, so the F = 64 case is fully unrolled (0.244 vs 0.261 ms per flow call with runtime loops).
+        auto gather_tile = [&](auto fcc, const int b, const int p0, const int rows_valid) {
+            constexpr int FC = decltype(fcc)::value;
+            const int fcv = FC ? FC : fc;
+            constexpr int CPL = FC ? (FC + 3) / 4 : 1;                  // chunks per lane and row (FC known)
+            // template block: the g distinct template rows of the tile are fetched once into a staging area (every row
+            // of a group repeats its template's 128 bytes) and replicated shared -> shared below
+            const bool staged = FLOW_STAGE_BYTES > 0 && g * fcv * 16 <= FLOW_STAGE_BYTES;       // CTA-uniform
+            if (staged) {
+                for (int i = lane; i < g * fcv; i += 32) {
+                    const int pr = i / fcv, c = i - pr * fcv;
+                    const bool ok = p0 + pr < n;
+                    ptx::cp_async16_cg(stage + i * 16,
+                                       reinterpret_cast<const uint4 *>(a.feat + ((size_t)b * n + (ok ? p0 + pr : 0)) * F) + c,
+                                       ok ? 16u : 0u);
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
+            // source block (and the template block when it is not staged): one gathered row per tile row
+#pragma unroll
+            for (int i = 0; i < RG; ++i) {
+                const bool ok = prow[i] < rows_valid;
+                const int src = ok ? __float_as_int(s_nbr[s * 128 + prow[i]].w) : 0;
+                const uint4 *ftp = reinterpret_cast<const uint4 *>(a.feat + ((size_t)b * n + (ok ? p0 + pgrp[i] : 0)) * F);
+                const uint4 *fsp = reinterpret_cast<const uint4 *>(a.feat + ((size_t)(a.B + b) * n + src) * F);
+                const uint32_t d = act + prow[i] * 16, nb = ok ? 16u : 0u;
+                if constexpr (FC > 0) {
+#pragma unroll
+                    for (int j = 0; j < CPL; ++j) {
+                        const int c = cq + 4 * j;
+                        if (FC % 4 == 0 || c < FC) {
+                            if (!staged) ptx::cp_async16_ca(d + c * TC_LBO, ftp + c, nb);
+                            ptx::cp_async16_cg(d + (FC + c) * TC_LBO, fsp + c, nb);
+                        }
+                    }
+                } else {
+                    for (int c = cq; c < fcv; c += 4) {
+                        if (!staged) ptx::cp_async16_ca(d + c * TC_LBO, ftp + c, nb);
+                        ptx::cp_async16_cg(d + (fcv + c) * TC_LBO, fsp + c, nb);
+                    }
+                }
+            }
+            if (staged) {
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                asm volatile("cp.async.wait_group 1;" ::: "memory");    // my part of the staging area has landed
+                __syncwarp();                                           // ... and every other lane's
+                if constexpr (FC > 0) {
+                    constexpr int BR = RG < 4 ? RG : 4;                 // row groups per batch: loads first, then stores
+#pragma unroll
+                    for (int i0 = 0; i0 < RG; i0 += BR) {
+                        uint32_t v[BR][CPL][4];
+#pragma unroll
+                        for (int i = 0; i < BR; ++i)
+#pragma unroll
+                            for (int j = 0; j < CPL; ++j) {
+                                const int c = cq + 4 * j;
+                                v[i][j][0] = v[i][j][1] = v[i][j][2] = v[i][j][3] = 0u;
+                                if (prow[i0 + i] < rows_valid && (FC % 4 == 0 || c < FC))
+                                    ld_shared_v4(stage + (pgrp[i0 + i] * FC + c) * 16, v[i][j][0], v[i][j][1], v[i][j][2],
+                                                 v[i][j][3]);
+                            }
+#pragma unroll
+                        for (int i = 0; i < BR; ++i)
+#pragma unroll
+                            for (int j = 0; j < CPL; ++j) {
+                                const int c = cq + 4 * j;
+                                if (FC % 4 == 0 || c < FC)
+                                    st_shared_v4(act + prow[i0 + i] * 16 + c * TC_LBO, v[i][j][0], v[i][j][1], v[i][j][2],
+                                                 v[i][j][3]);
+                            }
+                    }
+                } else {
+#pragma unroll 1
+                    for (int i = 0; i < RG; ++i) {
+                        const bool ok = prow[i] < rows_valid;
+                        for (int c = cq; c < fcv; c += 4) {
+                            uint32_t v0 = 0u, v1 = 0u, v2 = 0u, v3 = 0u;
+                            if (ok) ld_shared_v4(stage + (pgrp[i] * fcv + c) * 16, v0, v1, v2, v3);
+                            st_shared_v4(act + prow[i] * 16 + c * TC_LBO, v0, v1, v2, v3);
+                        }
+                    }
+                }
+                __syncwarp();                                           // the staging area is reused by the next tile
+            }
+        };
+        uint32_t iph = 0, fph = 0;
+        const int tile0 = blockIdx.x * FLOW_SLOTS + s;
+        for (int tile = tile0; tile < a.num_tiles; tile += tiles_per_iter) {
+            const int b = tile / a.tiles_per_pair;
+            const int p0 = (tile - b * a.tiles_per_pair) * g;
+            const int rows_valid = min(g, n - p0) * k;
+            ptx::mbar_wait(&idx_ready[s], iph & 1); ++iph;
+            if (tile != tile0) { ptx::mbar_wait(&act_free[s], fph & 1); ++fph; }
+            if (fc == 8) gather_tile(std::integral_constant<int, 8>{}, b, p0, rows_valid);   // F = 64: fully unrolled
+            else gather_tile(std::integral_constant<int, 0>{}, b, p0, rows_valid);
+            ptx::cp_async_wait_all();
+            ptx::fence_proxy_async_smem();
+            ptx::mbar_arrive(&gath[s]);
         }
     } else {
-        // ===================== row build + epilogues (8 warps per slot) =====================
+        // ===================== coordinates + epilogues (8 warps per slot) =====================
         // warp = (slot, column half, lane quarter): both halves of a quarter own the same 32 tile rows / TMEM lanes and
-        // split the columns (hidden layers), the operand chunks (row build) and the 128-channel blocks (last layer).
+        // split the columns (hidden layers) and the 128-channel blocks (last layer).
         const int s = warp / FLOW_WPS, half = (warp % FLOW_WPS) >> 2, q = warp & 3;
         const int r = q * 32 + lane;                                   // tile row == TMEM lane
         const uint32_t act = ptx::smem_u32(s_act + s * act_bytes);
@@ -373,60 +560,40 @@ flow_tc_kernel(FlowArgs a) {
         const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16) + s * 256;
         const int k = a.k, n = a.n, F = a.F, g = a.groups_per_tile;
         const int fc = F / 8;                                          // chunks per feature block
-        uint32_t dphase = 0;
+        uint32_t dphase = 0, iphase = 0, gphase = 0;
         [[maybe_unused]] int ft = -1;
         for (int tile = blockIdx.x * FLOW_SLOTS + s; tile < a.num_tiles; tile += tiles_per_iter) {
             ++ft;
             FLTRACE(0);
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * g;
-            // ---- build row r = (point p0 + r / k, neighbour r % k): [f_tmpl | f_src | dp hi,hi,lo | 0]
-            const int grp = r / k, j = r - grp * k;
-            const int pt = p0 + grp;
-            const bool valid = grp < g && pt < n;
-            bool masked = true;                                        // rows that do not exist never contribute
-            if (valid) {
-                const size_t trow = (size_t)b * n + pt;
-                // (prefetching this index one tile ahead was measured slower: 0.311 vs 0.297 ms, tools/ab.sh)
-                const int src = __ldg(a.nbr + trow * k + j);
-                const size_t srow = (size_t)(a.B + b) * n + src;
-                if (half == 0) {
-                    // 16-bit features are already operand bytes: one 16-byte chunk per load, all chunks in flight
-                    const uint4 *ft = reinterpret_cast<const uint4 *>(a.feat + trow * F);
-#pragma unroll 8
-                    for (int c = 0; c < fc; ++c) {
-                        const uint4 u = __ldg(ft + c);
-                        st_shared_v4(act_row + c * TC_LBO, u.x, u.y, u.z, u.w);
-                    }
-                    const float *pt3 = a.xyz + trow * 3, *ps3 = a.xyz + srow * 3;
-                    const float dx = __ldg(ps3) - __ldg(pt3), dy = __ldg(ps3 + 1) - __ldg(pt3 + 1),
-                                dz = __ldg(ps3 + 2) - __ldg(pt3 + 2);
+            const int rows_valid = min(g, n - p0) * k;
+            // ---- what these warps add to the rows: displacement chunks + radius mask (thread = row, half 0) from the
+            // row record in shared memory, zero K padding (half 1); then publish
+            uint32_t *maskw = s_maskw + ((ft & 1) * FLOW_SLOTS + s) * 4;    // by tile parity: written here, read in the
+                                                                       // last epilogue while fast warps may be a tile on
+            ptx::mbar_wait(&idx_ready[s], iphase & 1); ++iphase;
+            FLTRACE(11);
+            if (half == 0) {                                           // warp-uniform
+                bool masked = true;                                    // rows that do not exist never contribute
+                if (r < rows_valid) {
+                    const float4 rec = s_nbr[s * 128 + r];
+                    const float dx = rec.x, dy = rec.y, dz = rec.z;
                     store_coord_chunks<T16>(act_row + (2 * fc) * TC_LBO, act_row + (2 * fc + 1) * TC_LBO, dx, dy, dz);
                     // radius mask in fp32 on the raw displacement (deepclr.py:220-222)
                     masked = a.radius > 0.f && sqrtf(dx * dx + dy * dy + dz * dz) >= a.radius;
                 } else {
-                    const uint4 *fs = reinterpret_cast<const uint4 *>(a.feat + srow * F);
-#pragma unroll 8
-                    for (int c = 0; c < fc; ++c) {
-                        const uint4 u = __ldg(fs + c);
-                        st_shared_v4(act_row + (fc + c) * TC_LBO, u.x, u.y, u.z, u.w);
-                    }
-                    for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
-                }
-            } else {
-                const int cb = half == 0 ? 0 : fc, ce = half == 0 ? fc : 2 * fc;
-                for (int c = cb; c < ce; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
-                if (half == 0) {
                     st_shared_v4(act_row + (2 * fc) * TC_LBO, 0u, 0u, 0u, 0u);
                     st_shared_v4(act_row + (2 * fc + 1) * TC_LBO, 0u, 0u, 0u, 0u);
-                } else {
-                    for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
                 }
-            }
-            if (half == 0) {                                           // warp-uniform
                 const uint32_t mw = __ballot_sync(0xffffffffu, masked);
-                if (lane == 0) s_maskw[s * 4 + q] = mw;
+                if (lane == 0) maskw[q] = mw;
+            } else {
+                for (int c = 2 * fc + 2; c < K0p / 8; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
             }
+            FLTRACE(8);
+            ptx::mbar_wait(&gath[s], gphase & 1); ++gphase;            // the feature blocks have landed
+            FLTRACE(9);
             ptx::fence_proxy_async_smem();
             FLTRACE(1);
             ptx::mbar_arrive(&ready[s]);
@@ -455,7 +622,7 @@ flow_tc_kernel(FlowArgs a) {
             FLTRACE(6);
             uint32_t mk[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) mk[i] = s_maskw[s * 4 + i];
+            for (int i = 0; i < 4; ++i) mk[i] = maskw[i];
             for (int mb = half; mb < H3 / 128; mb += 2) {
                 const int ch = mb * 128 + r;
                 const float bias = s_bias[256 + ch];
@@ -786,8 +953,8 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     TC_CUDA(cudaMemcpy(t->flow_b + 128, sp[1].b, 128 * 4, cudaMemcpyDeviceToDevice));
     TC_CUDA(cudaMemcpy(t->flow_b + 256, sp[2].b, H3 * 4, cudaMemcpyDeviceToDevice));
     t->flow_smem = (size_t)128 * t->K0p * 2 + 128 * FLOW_K2P * 2 + (size_t)H3 * 128 * 2 +
-                   (size_t)FLOW_SLOTS * 128 * t->K0p * 2 + (256 + H3) * 4 + FLOW_SLOTS * 4 * 4 +
-                   (1 + 2 * FLOW_SLOTS) * 8 + 16;
+                   (size_t)FLOW_SLOTS * 128 * t->K0p * 2 + (256 + H3) * 4 + 2 * FLOW_SLOTS * 4 * 4 +
+                   (1 + 5 * FLOW_SLOTS) * 8 + 16 + FLOW_SLOTS * 128 * 16 + FLOW_SLOTS * FLOW_PROD * FLOW_STAGE_BYTES;
 
     // ---- head: tiles in (layer, 128-row block, 64-wide K block) order
     size_t head_elems = 0;
@@ -856,10 +1023,10 @@ int tc_convert(TcModel *t, const float *src, uint16_t *dst, size_t n, cudaStream
     return DCLR_OK;
 }
 
-int tc_flow(TcModel *t, const float *xyz, const uint16_t *feat, const int32_t *nbr, int B, int n, uint16_t *motion,
-            float *motion32, cudaStream_t st) {
+int tc_flow(TcModel *t, const uint16_t *feat, const float4 *nbr, int B, int n, uint16_t *motion, float *motion32,
+            cudaStream_t st) {
     FlowArgs fa;
-    fa.xyz = xyz; fa.feat = feat; fa.nbr = nbr; fa.w = t->flow_w; fa.bias = t->flow_b; fa.out = motion;
+    fa.feat = feat; fa.nbr = nbr; fa.w = t->flow_w; fa.bias = t->flow_b; fa.out = motion;
     fa.out32 = motion32;
     fa.B = B; fa.n = n; fa.k = t->k; fa.F = t->F; fa.K0p = t->K0p; fa.H3 = t->H3; fa.radius = t->radius;
     fa.groups_per_tile = 128 / t->k;

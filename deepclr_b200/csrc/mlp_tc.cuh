@@ -13,10 +13,11 @@ struct TcModel;
 int tc_create(const TcLayerSpec *specs, int F, int k, float radius, int fmt, TcModel **out);
 void tc_destroy(TcModel *t);
 // All activations that cross kernels are 16-bit images in the model's operand format (fp16 / bf16):
-// xyz [2B,n,3] fp32, feat16 [2B,n,F] point-major (templates first), nbr [B,n,k] -> motion16 [B*n, merge_out] features
-// only (the coordinates stay in xyz); motion32 (nullable) additionally receives the fp32 values for the API tap.
-int tc_flow(TcModel *t, const float *xyz, const uint16_t *feat16, const int32_t *nbr, int B, int n, uint16_t *motion16,
-            float *motion32, cudaStream_t st);
+// feat16 [2B,n,F] point-major (templates first), nbr [B,n,k] row records {source - template displacement, source index}
+// from knn_launch -> motion16 [B*n, merge_out] features only (the coordinates stay in xyz); motion32 (nullable)
+// additionally receives the fp32 values for the API tap.
+int tc_flow(TcModel *t, const uint16_t *feat16, const float4 *nbr, int B, int n, uint16_t *motion16, float *motion32,
+            cudaStream_t st);
 // motion16 [B*n, merge_out] + xyz [B*n,3] -> pooled [B, C_last] (max over the points); zero-fills pooled first
 int tc_head(TcModel *t, const float *xyz, const uint16_t *motion16, int B, int n, float *pooled, cudaStream_t st);
 // fp32 -> the model's 16-bit format, elementwise (features supplied by the caller: dclr_forward_features)

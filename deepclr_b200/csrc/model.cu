@@ -21,6 +21,7 @@ struct dclr_model {
     int last_launches = 0;
     // carved pointers (valid after ensure_ws)
     int32_t *fps_idx, *bq_idx[2], *bq_cnt[2], *knn_col;
+    float4 *knn_nbr4;          // [B,M,k] {source - template displacement, source index}: the flow kernel's row records
     void *bq_ws, *fps_ws;
     float *new_xyz, *sa_feat, *fps_temp, *rows, *h1, *h2, *h3, *motion, *actA, *actB, *pooled, *t1, *t2;
     uint8_t *mask;
@@ -75,11 +76,13 @@ static size_t carve(dclr_model *m, char *base, int G, int N, int B) {
         m->actA = (float *)take(BM * wmax * 4);
         m->actB = (float *)take(BM * wmax * 4);
         m->sa_feat16 = m->motion16 = nullptr;
+        m->knn_nbr4 = nullptr;
     } else {
         m->rows = m->h1 = m->h2 = m->h3 = m->actA = m->actB = nullptr;
         m->mask = nullptr;
         m->sa_feat16 = (uint16_t *)take((size_t)G * M * m->F * 2);
         m->motion16 = (uint16_t *)take(BM * a.merge_mlp[2] * 2);
+        m->knn_nbr4 = (float4 *)take(R * 16);
     }
     return off;
 }
@@ -173,13 +176,13 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
     // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
     {
         StageScope sc(m, ST_KNN, st);
-        DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, st));
+        DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, m->knn_nbr4, st));
     }
     if (m->numerics != 0) {
         {
             StageScope sc(m, ST_FLOW, st);
             // fp32 motion features only when the caller taps them; the head reads the 16-bit image
-            DCLR_TRY(tc_flow(m->tc, m->new_xyz, m->sa_feat16, m->knn_col, B, M, m->motion16,
+            DCLR_TRY(tc_flow(m->tc, m->sa_feat16, m->knn_nbr4, B, M, m->motion16,
                              motion_out ? m->motion : nullptr, st));
         }
         StageScope sc(m, ST_HEAD, st);

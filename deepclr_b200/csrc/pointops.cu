@@ -234,7 +234,8 @@ __device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
 
 __global__ void __launch_bounds__(KNN_WARPS * 32)
 knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
-           int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local) {
+           int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local,
+           float4 *__restrict__ nbr4) {
     __shared__ float s_c[KNN_TILE * 3];
     __shared__ uint64_t s_win[KNN_WARPS][KNN_MAXK];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -299,6 +300,10 @@ knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int
         if (row_out) row_out[o] = (int64_t)gy;
         if (col_out) col_out[o] = (int64_t)((size_t)b * Nx + ci);
         if (col_local) col_local[o] = (int32_t)ci;
+        if (nbr4) {
+            const float *c = xb + (size_t)ci * 3;
+            nbr4[o] = make_float4(__ldg(c) - qx, __ldg(c + 1) - qy, __ldg(c + 2) - qz, __int_as_float((int)ci));
+        }
     }
 }
 
@@ -315,7 +320,8 @@ constexpr int KNNF_CAP = 128;               // compacted candidates per query
 template <int KPL>
 __global__ void __launch_bounds__(KNNF_WARPS * 32)
 knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
-                int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local) {
+                int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local,
+                float4 *__restrict__ nbr4) {
     __shared__ float s_x[KPL * 32], s_y[KPL * 32], s_z[KPL * 32];
     __shared__ uint64_t s_cand[KNNF_WARPS][KNNF_CAP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -396,12 +402,14 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
                 if (row_out) row_out[o0 + r0] = (int64_t)gy;
                 if (col_out) col_out[o0 + r0] = (int64_t)((size_t)b * Nx + ci);
                 if (col_local) col_local[o0 + r0] = (int32_t)ci;
+                if (nbr4) nbr4[o0 + r0] = make_float4(s_x[ci] - qx, s_y[ci] - qy, s_z[ci] - qz, __int_as_float((int)ci));
             }
             if (lane + 32 < total && r1 < k) {
                 const uint32_t ci = (uint32_t)c1;
                 if (row_out) row_out[o0 + r1] = (int64_t)gy;
                 if (col_out) col_out[o0 + r1] = (int64_t)((size_t)b * Nx + ci);
                 if (col_local) col_local[o0 + r1] = (int32_t)ci;
+                if (nbr4) nbr4[o0 + r1] = make_float4(s_x[ci] - qx, s_y[ci] - qy, s_z[ci] - qz, __int_as_float((int)ci));
             }
             __syncwarp();
             continue;
@@ -436,6 +444,7 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
                 if (row_out) row_out[o0 + r] = (int64_t)gy;
                 if (col_out) col_out[o0 + r] = (int64_t)((size_t)b * Nx + ci);
                 if (col_local) col_local[o0 + r] = (int32_t)ci;
+                if (nbr4) nbr4[o0 + r] = make_float4(s_x[ci] - qx, s_y[ci] - qy, s_z[ci] - qz, __int_as_float((int)ci));
             }
         }
         __syncwarp();
@@ -443,16 +452,16 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
 }
 
 int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,
-               int32_t *col_local, cudaStream_t st) {
+               int32_t *col_local, float4 *nbr4, cudaStream_t st) {
     const dim3 fgrid(div_up(Ny, KNNF_WARPS * KNNF_QPW), B);
     if (k <= 32 && Nx <= 512) {
-        knn_fast_kernel<16><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        knn_fast_kernel<16><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
         DCLR_LAUNCH_CHECK("knn_fast_kernel");
     } else if (k <= 32 && Nx <= 1024) {
-        knn_fast_kernel<32><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        knn_fast_kernel<32><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
         DCLR_LAUNCH_CHECK("knn_fast_kernel");
     } else {
-        knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local);
+        knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
         DCLR_LAUNCH_CHECK("knn_kernel");
     }
     return DCLR_OK;
@@ -541,5 +550,5 @@ extern "C" int dclr_knn(const float *x, const float *y, int B, int Nx, int Ny, i
     DCLR_CHECK_ARG(k >= 1 && k <= Nx && k <= KNN_MAXK, "dclr_knn: need 1 <= k <= min(Nx,%d), got k=%d Nx=%d", KNN_MAXK,
                    k, Nx);
     if (B == 0 || Ny == 0) return DCLR_OK;
-    return knn_launch(x, y, B, Nx, Ny, k, row_out, col_out, nullptr, (cudaStream_t)stream);
+    return knn_launch(x, y, B, Nx, Ny, k, row_out, col_out, nullptr, nullptr, (cudaStream_t)stream);
 }

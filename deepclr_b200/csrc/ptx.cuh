@@ -45,6 +45,22 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 }
 
 // generic-proxy writes to smem -> visible to the async proxy (TMA / tcgen05.mma operand reads)
+// 4-byte asynchronous global->shared copy (LDGSTS) and "arrive on this mbarrier once my earlier cp.async have landed"
+// (.noinc: the arrival counts against the barrier's initial count)
+__device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void *src_gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
+}
+// 16-byte LDGSTS; src_bytes = 0 writes zeros (the source is not read).  .ca keeps the line in L1, .cg does not.
+__device__ __forceinline__ void cp_async16_ca(uint32_t dst_smem, const void *src_gmem, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src_gmem), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async16_cg(uint32_t dst_smem, const void *src_gmem, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src_gmem), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t *bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---- tcgen05 ----

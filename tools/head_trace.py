@@ -45,3 +45,6 @@ for i in range(8):
     if x[0] == 0:
         continue
     print(i, [int(x[j + 1] - x[j]) for j in range(7)], int(x[7] - x[0]), 'gap to next', int(f[i + 1][0] - x[7]) if i < 7 else '-')
+    if x[8]:
+        print('   build: record wait', int(x[11] - x[0]), '| coords+mask', int(x[8] - x[11]), '| wait for the gathered features',
+              int(x[9] - x[8]), '| proxy fence', int(x[1] - x[9]))
