@@ -296,7 +296,7 @@ size_t ball_grid_workspace_bytes(int B, int N) {
 
 int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
                      const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad, void *ws,
-                     cudaStream_t st, int *used) {
+                     cudaStream_t st, int *used, int phase) {
     *used = 0;
     const int words = (N + 31) / 32;
     int warps = (int)((200u * 1024u) / (((size_t)nr * words + BG_LIST) * 4));
@@ -318,8 +318,12 @@ int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, 
         DCLR_CUDA(cudaFuncSetAttribute(bq_grid_query_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done = true;
     }
-    bq_grid_build_kernel<<<B, BG_BUILD_T, BG_CELLS * sizeof(int), st>>>(pts, stride, N, rq, sorted, cellstart, params);
-    DCLR_LAUNCH_CHECK("bq_grid_build_kernel");
+    if (phase != BG_PHASE_QUERY) {
+        bq_grid_build_kernel<<<B, BG_BUILD_T, BG_CELLS * sizeof(int), st>>>(pts, stride, N, rq, sorted, cellstart, params);
+        DCLR_LAUNCH_CHECK("bq_grid_build_kernel");
+    }
+    *used = 1;
+    if (phase == BG_PHASE_BUILD) return DCLR_OK;
     BgQueryArgs a;
     a.new_xyz = new_xyz; a.sorted = sorted; a.cellstart = cellstart; a.params = params;
     a.N = N; a.M = M; a.nr = nr; a.pad = pad; a.warps = warps; a.rq = rq;

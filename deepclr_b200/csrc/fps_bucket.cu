@@ -345,13 +345,14 @@ static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int tie
 
 // *used = 0 when the shape is not handled (caller falls back to fps_launch)
 int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, void *ws,
-                      cudaStream_t st, int *used) {
+                      cudaStream_t st, int *used, cudaEvent_t after_sort) {
     *used = 0;
     const int tie_ref = fps_tie_rule() == 1;
     if (N <= 2048 || N > 131072 || npoint < 2) return DCLR_OK;
     float4 *sorted = (float4 *)ws;
     fps_sort_kernel<<<B, FS_T, 0, st>>>(pts, stride, N, sorted);
     DCLR_LAUNCH_CHECK("fps_sort_kernel");
+    if (after_sort) DCLR_CUDA(cudaEventRecord(after_sort, st));   // the sampling kernel leaves SMs idle: see model.cu
     int rc;
     if (N > 16384) {                    // point state in L2 (fps_bucket_l2.cu); block of the reference kernel = 1024
         rc = fps_bucket_l2_launch(sorted, (float *)(sorted + (size_t)B * N), B, N, npoint, tie_ref ? 10 : -1, idx, nx, st);

@@ -15,8 +15,9 @@ int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *
 size_t fps_bucket_workspace_bytes(int B, int N);
 int fps_bucket_l2_launch(const float4 *sorted, float *tmin, int B, int N, int npoint, int tieL, int32_t *idx, float *nx,
                          cudaStream_t st);
+// after_sort (optional) is recorded on st between the sort and the sampling kernel
 int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, void *ws,
-                      cudaStream_t st, int *used);
+                      cudaStream_t st, int *used, cudaEvent_t after_sort = nullptr);
 
 // pointops.cu
 int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
@@ -25,9 +26,12 @@ int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B,
 // ballgrid.cu: grid-accelerated ball query for large clouds; *used = 0 when the shape is not handled (then call
 // ball_query_launch).  ws must hold ball_grid_workspace_bytes(B, N) bytes.
 size_t ball_grid_workspace_bytes(int B, int N);
+// phase: the grid build reads only the cloud, so the model runs it on a side stream next to FPS (BG_PHASE_BUILD, new_xyz
+// unused) and the query after both (BG_PHASE_QUERY); *used is the same for every phase of a shape.
+enum { BG_PHASE_BOTH = 0, BG_PHASE_BUILD = 1, BG_PHASE_QUERY = 2 };
 int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,
                      const float *radii, const int *ns, int32_t *const *idx, int32_t *const *cnt, int pad, void *ws,
-                     cudaStream_t st, int *used);
+                     cudaStream_t st, int *used, int phase = BG_PHASE_BOTH);
 // nbr4 (optional) [B,Ny,k]: {x_cand - y_query (3 floats, the subtraction of the distance), candidate index bits} --
 // what the tensor-core flow kernel needs per row, in one aligned 16-byte record
 int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int64_t *row, int64_t *col,

@@ -30,6 +30,9 @@ struct dclr_model {
     // optional per-stage CUDA-event timing (dclr_model_set_timing): ring of calls x (stages + 1) events
     bool timing = false;
     cudaEvent_t *ev = nullptr;
+    // side stream: work that reads only the input cloud runs next to FPS (which leaves 20 of the 148 SMs idle)
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int ev_calls = 0;                // calls recorded since the last collect (may exceed the ring)
     int ev_cur = 0;                  // slot of the call being recorded
     uint32_t ev_mask[64] = {0};      // stages recorded per ring slot
@@ -136,20 +139,42 @@ struct StageScope {
 // FPS -> ball query (both radii, one pass) -> grouped MLP + max-pool.  pointnet2_modules.py:19-55
 static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cudaStream_t st) {
     const dclr_arch &a = m->arch;
+    // The ball-query grid build (counting sort of the cloud into cells, ~40 us for 128 KITTI clouds) depends on the
+    // input only, and the sampling kernel (one CTA per cloud, latency-bound) leaves SMs and issue slots idle for
+    // ~0.5 ms: fork the build onto a low-priority side stream once the FPS sort is done, join before the query.
+    if (!m->side) {
+        int lo = 0, hi = 0;
+        DCLR_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));     // lo = least priority
+        DCLR_CUDA(cudaStreamCreateWithPriority(&m->side, cudaStreamNonBlocking, lo));
+        DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+        DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
+    }
     {
         StageScope sc(m, ST_FPS, st);
         int used = 0;
-        DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_ws, st, &used));
+        DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_ws, st, &used, m->ev_fork));
         if (used) ++m->last_launches;                      // sort + sample
-        else DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+        else {
+            DCLR_CUDA(cudaEventRecord(m->ev_fork, st));
+            DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+        }
     }
     {
+        int grid_built = 0;
+        DCLR_CUDA(cudaStreamWaitEvent(m->side, m->ev_fork, 0));
+        DCLR_TRY(ball_grid_launch(nullptr, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples, m->bq_idx,
+                                  m->bq_cnt, /*pad=*/0, m->bq_ws, m->side, &grid_built, BG_PHASE_BUILD));
+        if (!grid_built) --m->last_launches;               // shape not handled by the grid: nothing was launched
+        DCLR_CUDA(cudaEventRecord(m->ev_join, m->side));
+    }
+    {
+        DCLR_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
         StageScope sc(m, ST_BALL, st);
         int used = 0;
         DCLR_TRY(ball_grid_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
-                                  m->bq_idx, m->bq_cnt, /*pad=*/0, m->bq_ws, st, &used));
-        if (used) ++m->last_launches;                      // build + query
-        else
+                                  m->bq_idx, m->bq_cnt, /*pad=*/0, m->bq_ws, st, &used, BG_PHASE_QUERY));
+        if (!used) --m->last_launches;
+        if (!used)
             DCLR_TRY(ball_query_launch(m->new_xyz, x, a.input_dim, G, N, a.npoint, a.num_scales, a.radii, a.nsamples,
                                        m->bq_idx, m->bq_cnt, /*pad=*/0, st));
     }
@@ -319,6 +344,9 @@ extern "C" void dclr_model_destroy(dclr_model *m) {
     }
     if (m->ws) cudaFree(m->ws);
     if (m->d_w) cudaFree(m->d_w);
+    if (m->ev_fork) cudaEventDestroy(m->ev_fork);
+    if (m->ev_join) cudaEventDestroy(m->ev_join);
+    if (m->side) cudaStreamDestroy(m->side);
     delete m;
 }
 
