@@ -33,6 +33,10 @@ int fail(int code, const char *fmt, ...);
             return ::dclr::fail(DCLR_E_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
     } while (0)
 
+// stream-ordered scratch memory for the op-level entry points (core.cu)
+int scratch_alloc(void **p, size_t bytes, cudaStream_t st);
+void scratch_free(void *p, cudaStream_t st);
+
 static inline int div_up(int a, int b) { return (a + b - 1) / b; }
 
 // The reference kernels' squared distance as nvcc contracts it (FMUL dy*dy, FFMA dx, FFMA dz): SURVEY.md App. A.

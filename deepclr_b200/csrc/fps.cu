@@ -259,17 +259,17 @@ extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoin
                    B, N, npoint, pt_stride);
     if (B == 0 || npoint == 0) return DCLR_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (N > 2048 && N <= 131072) {                         // exact pruned variants (fps_bucket.cu, fps_bucket_l2.cu)
+    if (N > 8192 && N <= 131072) {                         // exact pruned variants (fps_bucket.cu, fps_bucket_l2.cu)
         void *ws = nullptr;
-        DCLR_CUDA(cudaMallocAsync(&ws, fps_bucket_workspace_bytes(B, N), st));
+        { int rc_ = scratch_alloc(&ws, fps_bucket_workspace_bytes(B, N), st); if (rc_ != DCLR_OK) return rc_; }
         int used = 0;
         int rc = fps_bucket_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, ws, st, &used);
-        cudaFreeAsync(ws, st);
+        scratch_free(ws, st);
         if (rc != DCLR_OK || used) return rc;
     }
     float *temp = nullptr;
-    if (N > FPS_MAX_RESIDENT_N) DCLR_CUDA(cudaMallocAsync(&temp, (size_t)B * N * sizeof(float), st));
+    if (N > FPS_MAX_RESIDENT_N) { int rc_ = scratch_alloc((void **)&temp, (size_t)B * N * sizeof(float), st); if (rc_ != DCLR_OK) return rc_; }
     int rc = fps_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, temp, st);
-    if (temp) cudaFreeAsync(temp, st);
+    scratch_free(temp, st);
     return rc;
 }

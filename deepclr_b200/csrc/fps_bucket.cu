@@ -1,4 +1,4 @@
-// Bucketed farthest point sampling (2048 < N <= 16384): the selection of fps.cu with the N x npoint distance updates
+// Bucketed farthest point sampling (8192 < N <= 16384; up to 131072 with the point state in L2, fps_bucket_l2.cu): the selection of fps.cu with the N x npoint distance updates
 // pruned EXACTLY.
 //
 // The cloud is first put into Z-order (fps_sort_kernel: 64 x 64 Morton cells over the two widest axes, counting sort
@@ -348,7 +348,9 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
                       cudaStream_t st, int *used, cudaEvent_t after_sort) {
     *used = 0;
     const int tie_ref = fps_tie_rule() == 1;
-    if (N <= 2048 || N > 131072 || npoint < 2) return DCLR_OK;
+    static const int min_n = getenv("DCLR_FPS_BUCKET_MIN") ? atoi(getenv("DCLR_FPS_BUCKET_MIN")) : 8192;   // tuning knob; measured
+    // per 8 clouds, bucketed | resident kernel: N = 4096 0.154 | 0.118 ms, 8192 0.306 | 0.295, 12288 0.416 | 0.727
+    if (N <= min_n || N > 131072 || npoint < 2) return DCLR_OK;
     float4 *sorted = (float4 *)ws;
     fps_sort_kernel<<<B, FS_T, 0, st>>>(pts, stride, N, sorted);
     DCLR_LAUNCH_CHECK("fps_sort_kernel");
@@ -360,9 +362,16 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
         return rc;
     }
     static const int shape = getenv("DCLR_FPS_SHAPE") ? atoi(getenv("DCLR_FPS_SHAPE")) : 0;   // tuning knob (tools/)
-    if (N <= 4096) rc = launch_bucket<32, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    else if (N <= 8192) rc = launch_bucket<32, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    else if (shape == 32) rc = launch_bucket<32, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    // warps x buckets per warp (lane <-> bucket); fewer, fatter warps = cheaper block-wide argmax per round
+    if (N <= 4096) {
+        if (shape == 32) rc = launch_bucket<32, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+        else if (shape == 16) rc = launch_bucket<16, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+        else rc = launch_bucket<8, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    } else if (N <= 8192) {
+        if (shape == 32) rc = launch_bucket<32, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+        else if (shape == 16) rc = launch_bucket<16, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+        else rc = launch_bucket<8, 16>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    } else if (shape == 32) rc = launch_bucket<32, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     else if (shape == 16) rc = launch_bucket<16, 16>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     else rc = launch_bucket<8, 32>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     if (rc == DCLR_OK) *used = 1;

@@ -11,7 +11,8 @@ int fps_tie_rule();        // 0 = lowest index, 1 = the reference kernel's tree 
 int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, float *temp_big,
                cudaStream_t st);
 
-// fps_bucket.cu: exact pruned FPS for 2048 < N <= 16384; *used = 0 when the shape is not handled
+// fps_bucket.cu: exact pruned FPS for 8192 < N <= 131072 (smaller clouds: the resident kernel is faster); *used = 0
+// when the shape is not handled
 size_t fps_bucket_workspace_bytes(int B, int N);
 int fps_bucket_l2_launch(const float4 *sorted, float *tmin, int B, int N, int npoint, int tieL, int32_t *idx, float *nx,
                          cudaStream_t st);

@@ -532,10 +532,10 @@ extern "C" int dclr_ball_query(const float *new_xyz, const float *pts, int pt_st
     cudaStream_t st = (cudaStream_t)stream;
     if (N >= 2048) {                                       // large clouds: uniform-grid candidate pruning (ballgrid.cu)
         void *ws = nullptr;
-        DCLR_CUDA(cudaMallocAsync(&ws, ball_grid_workspace_bytes(B, N), st));
+        { int rc_ = scratch_alloc(&ws, ball_grid_workspace_bytes(B, N), st); if (rc_ != DCLR_OK) return rc_; }
         int used = 0;
         int rc = ball_grid_launch(new_xyz, pts, pt_stride, B, N, M, 1, &radius, &nsample, idx, cnt, pad, ws, st, &used);
-        cudaFreeAsync(ws, st);
+        scratch_free(ws, st);
         if (rc != DCLR_OK || used) return rc;
     }
     return ball_query_launch(new_xyz, pts, pt_stride, B, N, M, 1, &radius, &nsample, idx, cnt, pad,
