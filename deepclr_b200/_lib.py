@@ -32,6 +32,10 @@ _SIGNATURES = {
     'dclr_gather': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_pose_to_matrix': (c_int, [c_void_p, c_int, c_int, ctypes.c_float, c_void_p, c_void_p]),
     'dclr_pose_errors': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    'dclr_filter_clouds': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_float,
+                                   c_void_p, c_void_p, c_void_p]),
+    'dclr_subsample_clouds': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, ctypes.c_uint64, c_int,
+                                      c_void_p, c_void_p, c_void_p, c_void_p]),
     'dclr_gather_grad': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_group_grad': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_ball_query': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p,

@@ -1,0 +1,254 @@
+// Pre-processing in front of the forward, batched on the device over a RAGGED batch of raw scans:
+//   filter_clouds_kernel   SystematicErasing (cloud[start::nth], deepclr/data/transforms/transforms.py:244-268)
+//                          -> RangeSelection (max(|x|,|y|) in [min,max], :90-113) -> TruncateDimension (:271-283),
+//                          the order of deepclr/data/transforms/build.py:23-24,37-38; order-preserving compaction
+//   subsample_clouds_kernel size-equalising random subsample into the dense [num_clouds, N, C] batch the forward reads
+//                          (ModelInferenceHelper.stack, deepclr/models/base.py:130-135: cloud[randperm(n)[:N]];
+//                          RandomErasing max_points, transforms.py:128-131)
+// The reference does all of this per cloud in numpy on the host and then copies the result; here the raw scans are
+// uploaded once and never come back.
+//
+// Both kernels are HBM-bound byte movers.  The filter is ONE pass: a tile of 2048 points is loaded (one float4 per
+// point), its keep flags are ranked with ballots + a 64-segment scan, and the tile's place in the output comes from a
+// chained scan over the tiles of its cloud -- one 64-bit word per cloud {next tile, points kept so far}.  Tiles are
+// handed out by an atomic ticket, so the CTA holding ticket t-1 is always already running when ticket t waits for it.
+// Algorithmic bytes: 4 C_in n read + 4 C_out kept written.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace dclr {
+
+constexpr int FLT_THREADS = 256;
+constexpr int FLT_ROWS = 8;
+constexpr int FLT_TILE = FLT_THREADS * FLT_ROWS;   // 2048 points = 32 KB of float4
+constexpr int FLT_SEGS = FLT_ROWS * (FLT_THREADS / 32);
+
+struct FilterArgs {
+    int nth, start;          // keep i iff i >= start && (i - start) % nth == 0
+    float rmin, rmax;        // then keep iff rmin <= max(|x|,|y|) <= rmax (fp32 compare, NaN coordinates drop)
+    int use_range;           // the reference returns the cloud untouched for (0, inf)
+};
+
+__device__ __forceinline__ bool keep_point(int i, float x, float y, const FilterArgs &f) {
+    bool k = true;
+    if (f.nth > 1) k = (i >= f.start) && ((i - f.start) % f.nth == 0);
+    else k = i >= f.start;
+    if (f.use_range) {
+        const float m = fmaxf(fabsf(x), fabsf(y));
+        k = k && (x == x) && (y == y) && (m >= f.rmin) && (m <= f.rmax);   // np.max propagates NaN -> both tests false
+    }
+    return k;
+}
+
+__device__ __forceinline__ unsigned long long ld_chain(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_chain(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// grid (max_tiles, B).  VEC4: C_in == C_out == 4, rows are float4.
+template <bool VEC4>
+__global__ void __launch_bounds__(FLT_THREADS)
+filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ offsets, int C_in, int C_out,
+                     FilterArgs f, float *__restrict__ out, int32_t *__restrict__ counts,
+                     unsigned *__restrict__ ticket, unsigned long long *__restrict__ chain) {
+    __shared__ int s_seg[FLT_SEGS];
+    __shared__ unsigned s_ticket;
+    __shared__ int s_base;
+    const int b = blockIdx.y;
+    const int row0 = offsets[b];
+    const int n = offsets[b + 1] - row0;
+    const int ntiles = (n + FLT_TILE - 1) / FLT_TILE;
+    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  for (;;) {   // a CTA keeps taking tiles of its cloud: max_points only sizes the grid, any cloud length is handled
+    __syncthreads();   // s_ticket / s_seg / s_base of the previous tile are no longer read
+    if (threadIdx.x == 0) s_ticket = atomicAdd(&ticket[b], 1u);
+    __syncthreads();
+    const unsigned t = s_ticket;
+    if ((int)t >= ntiles) {
+        if (t == 0 && threadIdx.x == 0) counts[b] = 0;   // empty cloud
+        return;
+    }
+    const int i0 = (int)t * FLT_TILE + (int)threadIdx.x;
+
+    float4 v[FLT_ROWS];
+    unsigned keep_bits = 0, rank_bits[2] = {0, 0};   // 8 ranks of 5 bits + the keep flag each
+#pragma unroll
+    for (int r = 0; r < FLT_ROWS; ++r) {
+        const int i = i0 + r * FLT_THREADS;
+        bool k = false;
+        if (i < n) {
+            if (VEC4) {
+                v[r] = __ldg(reinterpret_cast<const float4 *>(pts) + (size_t)(row0 + i));
+                k = keep_point(i, v[r].x, v[r].y, f);
+            } else {
+                const float *p = pts + (size_t)(row0 + i) * C_in;
+                k = keep_point(i, __ldg(p), __ldg(p + 1), f);
+            }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, k);
+        if (lane == 0) s_seg[r * (FLT_THREADS / 32) + warp] = __popc(bal);
+        const unsigned rk = __popc(bal & ((1u << lane) - 1u));
+        keep_bits |= (k ? 1u : 0u) << r;
+        rank_bits[r >> 2] |= rk << ((r & 3) * 8);
+    }
+    __syncthreads();
+    if (warp == 0) {
+        // exclusive scan of the 64 segment counts (row-major: all warps of row 0, then row 1 ...), 2 per lane
+        const int a = s_seg[2 * lane], c = s_seg[2 * lane + 1];
+        int incl = a + c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((int)lane >= d) incl += o;
+        }
+        const int excl = incl - (a + c);
+        s_seg[2 * lane] = excl;
+        s_seg[2 * lane + 1] = excl + a;
+        if (lane == 31) {
+            // chained scan: wait for the previous tile of this cloud, take its running total, pass ours on
+            unsigned long long w = ld_chain(chain + b);
+            while ((unsigned)(w >> 32) != t) {
+                __nanosleep(32);
+                w = ld_chain(chain + b);
+            }
+            const unsigned base = (unsigned)w;
+            st_chain(chain + b, ((unsigned long long)(t + 1) << 32) | (unsigned long long)(base + (unsigned)incl));
+            s_base = (int)base;
+            if ((int)t == ntiles - 1) counts[b] = (int)base + incl;
+        }
+    }
+    __syncthreads();
+    const int base = s_base;
+#pragma unroll
+    for (int r = 0; r < FLT_ROWS; ++r) {
+        if (!((keep_bits >> r) & 1u)) continue;
+        const int rk = (rank_bits[r >> 2] >> ((r & 3) * 8)) & 0xff;
+        const size_t dst = (size_t)row0 + base + s_seg[r * (FLT_THREADS / 32) + warp] + rk;
+        if (VEC4) {
+            reinterpret_cast<float4 *>(out)[dst] = v[r];
+        } else {
+            const float *p = pts + (size_t)(row0 + i0 + r * FLT_THREADS) * C_in;
+            for (int c = 0; c < C_out; ++c) out[dst * C_out + c] = __ldg(p + c);
+        }
+    }
+  }
+}
+
+// ---- keyed permutation of [0, n): balanced Feistel network on an even number of bits >= log2 n, cycle walking back
+// into the domain (expected < 4 walks).  A bijection by construction, so the first N values are N distinct rows.
+__device__ __forceinline__ unsigned mix32(unsigned x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ unsigned feistel_perm(unsigned j, unsigned n, unsigned key) {
+    if (n <= 1) return 0;
+    int bits = 32 - __clz(n - 1);
+    bits = (bits + 1) & ~1;
+    if (bits < 2) bits = 2;
+    const int half = bits >> 1;
+    const unsigned mask = (1u << half) - 1u;
+    unsigned x = j;
+    do {
+        unsigned L = x >> half, R = x & mask;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            const unsigned F = mix32(R ^ (key + 0x9e3779b9u * (unsigned)(r + 1))) & mask;
+            const unsigned nl = R;
+            R = L ^ F;
+            L = nl;
+        }
+        x = (L << half) | R;
+    } while (x >= n);
+    return x;
+}
+
+// grid (ceil(N_out / 256), B)
+template <bool VEC4>
+__global__ void __launch_bounds__(256)
+subsample_clouds_kernel(const float *__restrict__ in, const int32_t *__restrict__ offsets,
+                        const int32_t *__restrict__ counts, int C_in, int C_out, int N_out, unsigned seed_lo,
+                        unsigned seed_hi, int ordered_if_equal, float *__restrict__ x_out, int32_t *__restrict__ perm_out,
+                        int32_t *__restrict__ short_out) {
+    const int b = blockIdx.y;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N_out) return;
+    const int row0 = offsets[b];
+    const int n = counts ? counts[b] : offsets[b + 1] - row0;
+    int src = -1;
+    if (n > 0) {
+        if (n == N_out && ordered_if_equal) src = j;   // the reference leaves equal-sized clouds in order
+        else src = (int)feistel_perm((unsigned)(j % n), (unsigned)n, mix32(seed_lo ^ mix32(seed_hi + (unsigned)b)));
+    }
+    if (n < N_out && j == 0 && short_out) atomicAdd(short_out, 1);
+    const size_t dst = (size_t)b * N_out + j;
+    if (perm_out) perm_out[dst] = src;
+    if (VEC4) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (src >= 0) v = __ldg(reinterpret_cast<const float4 *>(in) + (size_t)(row0 + src));
+        reinterpret_cast<float4 *>(x_out)[dst] = v;
+    } else {
+        for (int c = 0; c < C_out; ++c)
+            x_out[dst * C_out + c] = src >= 0 ? __ldg(in + (size_t)(row0 + src) * C_in + c) : 0.f;
+    }
+}
+
+}  // namespace dclr
+
+using namespace dclr;
+
+extern "C" int dclr_filter_clouds(const float *pts, const int32_t *offsets, int B, int max_points, int C_in, int C_out,
+                                  int nth, int start, float min_range, float max_range, float *out,
+                                  int32_t *counts_out, void *stream) {
+    DCLR_CHECK_ARG(B >= 0 && max_points >= 0, "dclr_filter_clouds: B and max_points must be >= 0");
+    if (B == 0) return DCLR_OK;
+    DCLR_CHECK_ARG(pts && offsets && out && counts_out, "dclr_filter_clouds: null pointer");
+    DCLR_CHECK_ARG(C_in >= 2 && C_out >= 1 && C_out <= C_in, "dclr_filter_clouds: need 2 <= C_in, 1 <= C_out <= C_in (got %d, %d)", C_in, C_out);
+    DCLR_CHECK_ARG(nth >= 1 && start >= 0 && start < nth, "dclr_filter_clouds: need nth >= 1 and 0 <= start < nth (got %d, %d)", nth, start);
+    DCLR_CHECK_ARG(B <= 65535, "dclr_filter_clouds: at most 65535 clouds per call");
+    DCLR_CHECK_ARG(!(min_range != min_range) && !(max_range != max_range), "dclr_filter_clouds: NaN range");
+    cudaStream_t st = (cudaStream_t)stream;
+    FilterArgs f;
+    f.nth = nth; f.start = start; f.rmin = min_range; f.rmax = max_range;
+    f.use_range = !(min_range == 0.0f && isinf(max_range) && max_range > 0);
+    // per-cloud chain word (8 B) + ticket (4 B), zeroed per call
+    void *ws = nullptr;
+    const size_t chain_bytes = (size_t)B * 8, ws_bytes = chain_bytes + (size_t)B * 4;
+    int rc = scratch_alloc(&ws, ws_bytes, st);
+    if (rc != DCLR_OK) return rc;
+    cudaError_t e = cudaMemsetAsync(ws, 0, ws_bytes, st);
+    if (e != cudaSuccess) { scratch_free(ws, st); return fail(DCLR_E_CUDA, "dclr_filter_clouds: memset: %s", cudaGetErrorString(e)); }
+    auto *chain = (unsigned long long *)ws;
+    auto *ticket = (unsigned *)((char *)ws + chain_bytes);
+    const int tiles = max_points > 0 ? div_up(max_points, FLT_TILE) : 1;
+    dim3 grid(tiles, B);
+    const bool vec4 = C_in == 4 && C_out == 4 && ((uintptr_t)pts % 16 == 0) && ((uintptr_t)out % 16 == 0);
+    if (vec4) filter_clouds_kernel<true><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, C_in, C_out, f, out, counts_out, ticket, chain);
+    else filter_clouds_kernel<false><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, C_in, C_out, f, out, counts_out, ticket, chain);
+    e = cudaGetLastError();
+    scratch_free(ws, st);
+    if (e != cudaSuccess) return fail(DCLR_E_CUDA, "launch of filter_clouds_kernel failed: %s", cudaGetErrorString(e));
+    return DCLR_OK;
+}
+
+extern "C" int dclr_subsample_clouds(const float *pts, const int32_t *offsets, const int32_t *counts, int B, int C_in,
+                                     int C_out, int N_out, uint64_t seed, int ordered_if_equal, float *x_out,
+                                     int32_t *perm_out, int32_t *short_out, void *stream) {
+    DCLR_CHECK_ARG(B >= 0 && N_out >= 0, "dclr_subsample_clouds: B and N_out must be >= 0");
+    if (B == 0 || N_out == 0) return DCLR_OK;
+    DCLR_CHECK_ARG(pts && offsets && x_out, "dclr_subsample_clouds: null pointer");
+    DCLR_CHECK_ARG(C_in >= 1 && C_out >= 1 && C_out <= C_in, "dclr_subsample_clouds: need 1 <= C_out <= C_in (got %d, %d)", C_out, C_in);
+    DCLR_CHECK_ARG(B <= 65535, "dclr_subsample_clouds: at most 65535 clouds per call");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (short_out) DCLR_CUDA(cudaMemsetAsync(short_out, 0, sizeof(int32_t), st));
+    dim3 grid(div_up(N_out, 256), B);
+    const bool vec4 = C_in == 4 && C_out == 4 && ((uintptr_t)pts % 16 == 0) && ((uintptr_t)x_out % 16 == 0);
+    const unsigned lo = (unsigned)seed, hi = (unsigned)(seed >> 32);
+    if (vec4) subsample_clouds_kernel<true><<<grid, 256, 0, st>>>(pts, offsets, counts, C_in, C_out, N_out, lo, hi, ordered_if_equal, x_out, perm_out, short_out);
+    else subsample_clouds_kernel<false><<<grid, 256, 0, st>>>(pts, offsets, counts, C_in, C_out, N_out, lo, hi, ordered_if_equal, x_out, perm_out, short_out);
+    DCLR_LAUNCH_CHECK("subsample_clouds_kernel");
+    return DCLR_OK;
+}

@@ -84,6 +84,15 @@ class ModelInferenceHelper:
     def stack(template: torch.Tensor, source: torch.Tensor) -> torch.Tensor:
         """[2, N, C] batch, template first; the larger cloud is randomly reduced to the smaller size."""
         n = min(template.shape[0], source.shape[0])
+        if template.is_cuda and source.is_cuda and template.shape[0] != source.shape[0]:
+            # device-resident clouds: one native subsample kernel writes the [2, n, C] batch (no host permutation,
+            # no index upload); the smaller cloud keeps its order as in the reference
+            from ..data import device as dev_ops
+            lengths = [int(template.shape[0]), int(source.shape[0])]
+            rc = dev_ops.RaggedClouds(torch.cat((template, source), 0).float(),
+                                      torch.tensor([0, lengths[0], lengths[0] + lengths[1]], dtype=torch.int32,
+                                                   device=template.device), lengths)
+            return dev_ops.subsample_clouds(rc, n, seed=int(torch.randint(0, 2 ** 62, (1,)).item()))
         if source.shape[0] > n:
             source = source[torch.randperm(source.shape[0])[:n], :]
         elif template.shape[0] > n:

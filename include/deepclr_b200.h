@@ -175,6 +175,31 @@ int dclr_pose_to_matrix(const float *labels, int B, int label_type, float scale,
  * of the translation part. */
 int dclr_pose_errors(const double *T1, const double *T2, int B, double *rot_rad_out, double *trans_out, void *stream);
 
+/* ------------------------------------------------------------------ pre-processing on the device
+ * A ragged batch of raw scans: pts [total, C_in] fp32 = the clouds back to back, offsets [B+1] i32 (DEVICE) = first
+ * row of each cloud, offsets[B] = total.
+ *
+ * dclr_filter_clouds: SystematicErasing(nth, start) (cloud[start::nth], deepclr/data/transforms/transforms.py:244-268)
+ * -> RangeSelection(min_range, max_range) (keep rows with min <= max(|x|,|y|) <= max compared in fp32, rows with a NaN
+ * in x or y drop; (0, +inf) = no test at all, as the reference returns the cloud untouched; :90-113) ->
+ * TruncateDimension(C_out) (:271-283) -- the chain of deepclr/data/transforms/build.py:23-24,37-38 -- as one
+ * order-preserving compaction per cloud.  Cloud b's surviving rows are written to out [total, C_out] from row
+ * offsets[b] on (same offsets as the input; out may not alias pts), their number to counts_out[b].  start = -1 (random
+ * start) is drawn by the caller.  max_points (an upper bound of the largest cloud) only sizes the grid. */
+int dclr_filter_clouds(const float *pts, const int32_t *offsets, int B, int max_points, int C_in, int C_out, int nth,
+                       int start, float min_range, float max_range, float *out, int32_t *counts_out, void *stream);
+/* dclr_subsample_clouds: N_out distinct random rows of every cloud into the dense batch the forward reads,
+ * x_out [B, N_out, C_out] -- ModelInferenceHelper.stack (deepclr/models/base.py:130-135: cloud[randperm(n)[:N_out]])
+ * and RandomErasing(max_points) (transforms.py:128-131), batched.  Cloud b = rows offsets[b] .. + n_b with
+ * n_b = counts[b] (counts = NULL: offsets[b+1] - offsets[b]).  Row j of cloud b is source row P_b(j), P_b a keyed
+ * bijection of [0, n_b) (6-round balanced Feistel network + cycle walking; key from seed and b), so the rows are
+ * distinct; n_b == N_out with ordered_if_equal != 0 copies the cloud in order (the reference does not permute equal
+ * sizes).  n_b < N_out: rows j >= n_b repeat P_b(j mod n_b) and *short_out (optional, DEVICE i32) counts such clouds;
+ * n_b == 0 gives zeros and perm -1.  perm_out (optional) [B, N_out] i32 = the chosen source rows. */
+int dclr_subsample_clouds(const float *pts, const int32_t *offsets, const int32_t *counts, int B, int C_in, int C_out,
+                          int N_out, uint64_t seed, int ordered_if_equal, float *x_out, int32_t *perm_out,
+                          int32_t *short_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

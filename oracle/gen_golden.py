@@ -86,11 +86,50 @@ def ops_case():
           '| degenerate agree =', np.array_equal(ops.fps(small, 128), ops.fps_lowidx(small, 128)))
 
 
+def preproc_case():
+    """Ragged pre-processing fixtures made by the reference's OWN transform classes (SystematicErasing, RangeSelection,
+    TruncateDimension: deepclr/data/transforms/transforms.py:90-113,244-283) in the order of transforms/build.py:37-38;
+    the numpy restatement in oracle/preproc.py is checked against them here."""
+    import importlib
+    from oracle import preproc
+    ref_import.load()
+    T = importlib.import_module('deepclr.data.transforms.transforms')
+    rng = np.random.Generator(np.random.PCG64(7))
+    sizes = [5000, 0, 2048, 1, 4097, 333]
+    clouds = []
+    for n in sizes:
+        c = rng.uniform(-60, 60, (n, 5)).astype(np.float32)
+        c[:, 2] = rng.uniform(-3, 3, n)
+        clouds.append(c)
+    clouds[0][10, 0] = np.nan                       # NaN coordinate: dropped by the range test
+    clouds[0][20, :2] = [2.0, -1.0]                 # max(|x|,|y|) exactly on the lower bound: kept
+    clouds[0][24, :2] = [-50.0, 3.0]                # exactly on the upper bound: kept
+    clouds[0][28, :2] = [np.nextafter(np.float32(2.0), np.float32(0)), 0.5]     # just inside the hole: dropped
+    out = {}
+    cfgs = [dict(nth=1, start=0, rmin=0.0, rmax=np.inf, dim=4), dict(nth=2, start=0, rmin=2.0, rmax=50.0, dim=4),
+            dict(nth=3, start=2, rmin=0.0, rmax=30.0, dim=3), dict(nth=1, start=0, rmin=5.0, rmax=np.inf, dim=5)]
+    for ci, c in enumerate(cfgs):
+        chain = [T.SystematicErasing(c['nth'], c['start']), T.RangeSelection(c['rmin'], c['rmax'], dim=3),
+                 T.TruncateDimension(c['dim'])]
+        sample = {'clouds': [x.copy() for x in clouds]}
+        for t in chain:
+            sample = t(sample)
+        for b, (ref_out, raw) in enumerate(zip(sample['clouds'], clouds)):
+            mine = preproc.filter_cloud(raw, c['nth'], c['start'], c['rmin'], c['rmax'], c['dim'])
+            assert np.array_equal(ref_out, mine, equal_nan=True), (ci, b)
+            out[f'out_{ci}_{b}'] = np.ascontiguousarray(ref_out)
+        out[f'cfg_{ci}'] = np.array([c['nth'], c['start'], c['rmin'], c['rmax'], c['dim']], np.float64)
+    np.savez_compressed(os.path.join(GOLDEN, 'preproc_small.npz'), num_cfgs=len(cfgs), num_clouds=len(clouds),
+                        **{f'cloud_{b}': c for b, c in enumerate(clouds)}, **out)
+    print('preproc_small: restatement == reference transforms on', len(cfgs), 'configs x', len(clouds), 'clouds')
+
+
 def main():
     if not ref_import.available():
         raise SystemExit('reference tree not mounted; goldens can only be generated in the build container')
     os.makedirs(GOLDEN, exist_ok=True)
     ops_case()
+    preproc_case()
     for case in CASES:
         run_case(*case)
 

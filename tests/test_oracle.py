@@ -100,3 +100,31 @@ def test_model_oracle_reproduces_reference_goldens(case):
     assert bool(g['fps_rules_agree'])          # reference block-tree tie-break == lowest-index on these inputs
     rot, trans = model_oracle.pose_errors(y[0], g['y'][0])
     assert rot < 1e-3 and trans < 1e-5
+
+
+def test_preproc_restatement_matches_reference_transform_goldens():
+    """tests/golden/preproc_small.npz holds the outputs of the reference's own SystematicErasing -> RangeSelection ->
+    TruncateDimension classes (oracle/gen_golden.py:preproc_case)."""
+    from oracle import preproc
+    g = load_golden('preproc_small')
+    for ci in range(int(g['num_cfgs'])):
+        nth, start, rmin, rmax, dim = g[f'cfg_{ci}']
+        for b in range(int(g['num_clouds'])):
+            got = preproc.filter_cloud(g[f'cloud_{b}'], int(nth), int(start), float(rmin), float(rmax), int(dim))
+            assert np.array_equal(got, g[f'out_{ci}_{b}'], equal_nan=True), (ci, b)
+    out = g['out_1_0']
+    assert not np.isnan(out[:, :2]).any()                       # the NaN row dropped
+    assert (out[:, :2] == np.float32([2.0, -1.0])).all(1).any() and (out[:, :2] == np.float32([-50.0, 3.0])).all(1).any()
+
+
+def test_feistel_permutation_is_a_bijection():
+    from oracle import preproc
+    for n in (1, 2, 3, 5, 16, 17, 255, 256, 257, 1000, 4097):
+        for b in (0, 3):
+            key = preproc.cloud_key(99, b)
+            img = sorted(preproc.feistel_perm(j, n, key) for j in range(n))
+            assert img == list(range(n)), n
+    a = preproc.subsample_rows(1000, 100, 1, 0)
+    assert len(set(a.tolist())) == 100 and not np.array_equal(a, preproc.subsample_rows(1000, 100, 2, 0))
+    assert np.array_equal(preproc.subsample_rows(100, 100, 1, 0), np.arange(100))
+    assert np.array_equal(preproc.subsample_rows(0, 4, 1, 0), np.full(4, -1))
