@@ -62,6 +62,13 @@ class RaggedClouds:
         torch.cat(ts, 0, out=stage)
         return RaggedClouds(stage.to(device, non_blocking=True), off.to(device, non_blocking=True), lengths)
 
+    @staticmethod
+    def from_staged(stage: torch.Tensor, lengths, device) -> 'RaggedClouds':
+        """stage: [total, C] float32 host tensor holding the clouds back to back (datasets.stage_scans)."""
+        off = torch.zeros(len(lengths) + 1, dtype=torch.int32)
+        off[1:] = torch.cumsum(torch.tensor(list(lengths), dtype=torch.int64), 0).to(torch.int32)
+        return RaggedClouds(stage.to(device, non_blocking=True), off.to(device, non_blocking=True), lengths)
+
     def __len__(self) -> int:
         return len(self.lengths)
 

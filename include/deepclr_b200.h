@@ -185,7 +185,8 @@ int dclr_pose_errors(const double *T1, const double *T2, int B, double *rot_rad_
  * TruncateDimension(C_out) (:271-283) -- the chain of deepclr/data/transforms/build.py:23-24,37-38 -- as one
  * order-preserving compaction per cloud.  Cloud b's surviving rows are written to out [total, C_out] from row
  * offsets[b] on (same offsets as the input; out may not alias pts), their number to counts_out[b].  start = -1 (random
- * start) is drawn by the caller.  max_points (an upper bound of the largest cloud) only sizes the grid. */
+ * start) is drawn by the caller.  max_points = an upper bound of the largest cloud (it sizes the grid and the per-tile
+ * scratch); a cloud that is longer is not processed and gets counts_out[b] = -1. */
 int dclr_filter_clouds(const float *pts, const int32_t *offsets, int B, int max_points, int C_in, int C_out, int nth,
                        int start, float min_range, float max_range, float *out, int32_t *counts_out, void *stream);
 /* dclr_subsample_clouds: N_out distinct random rows of every cloud into the dense batch the forward reads,

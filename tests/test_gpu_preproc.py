@@ -54,19 +54,21 @@ def test_filter_full_size_scans_bit_exact(dev_ops, C, nth, start, rmin, rmax):
         assert np.array_equal(_rows(out, b), want)
 
 
-def test_filter_grid_smaller_than_the_cloud(dev_ops):
-    """max_points only sizes the grid: a CTA keeps taking tiles, so an under-estimate is still correct."""
+def test_filter_cloud_longer_than_max_points_is_reported(dev_ops):
+    """max_points sizes the grid and the tile status array: a longer cloud is not processed, its count reads -1, the
+    other clouds of the call are unaffected."""
     from deepclr_b200 import _lib
     rng = np.random.Generator(np.random.PCG64(3))
-    c = rng.uniform(-80, 80, (50000, 4)).astype(np.float32)
+    c = rng.uniform(-80, 80, (50000 + 3000, 4)).astype(np.float32)
     pts = torch.from_numpy(c).to(DEV)
-    off = torch.tensor([0, 50000], dtype=torch.int32, device=DEV)
+    off = torch.tensor([0, 50000, 53000], dtype=torch.int32, device=DEV)
     out = torch.empty_like(pts)
-    cnt = torch.empty(1, dtype=torch.int32, device=DEV)
-    _lib.check(_lib.lib().dclr_filter_clouds(_lib.ptr(pts), _lib.ptr(off), 1, 3000, 4, 4, 2, 0, 2.0, 50.0,
+    cnt = torch.empty(2, dtype=torch.int32, device=DEV)
+    _lib.check(_lib.lib().dclr_filter_clouds(_lib.ptr(pts), _lib.ptr(off), 2, 3000, 4, 4, 2, 0, 2.0, 50.0,
                                              _lib.ptr(out), _lib.ptr(cnt), _lib.stream_ptr()), 'dclr_filter_clouds')
-    want = preproc.filter_cloud(c, 2, 0, 2.0, 50.0)
-    assert int(cnt) == want.shape[0] and np.array_equal(out[:int(cnt)].cpu().numpy(), want)
+    want = preproc.filter_cloud(c[50000:], 2, 0, 2.0, 50.0)
+    assert int(cnt[0]) == -1
+    assert int(cnt[1]) == want.shape[0] and np.array_equal(out[50000:50000 + int(cnt[1])].cpu().numpy(), want)
 
 
 def test_filter_argument_errors(dev_ops):

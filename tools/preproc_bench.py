@@ -21,7 +21,7 @@ from oracle import preproc  # noqa: E402
 def hbm_peak():
     try:
         p = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
-        for k in ('hbm_gbps_burst', 'hbm_copy_gbps_burst', 'hbm_gbps', 'hbm_copy_gbps'):
+        for k in ('hbm_gbs', 'hbm_gbps'):
             if k in p:
                 return float(p[k]), k
         for k, v in p.items():
