@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'fp16'), choices=['fp32', 'fp16', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-latency', action='store_true', help='skip the batch-1 latency loop (ncu launch lists)')
+    ap.add_argument('--no-raw-scans', action='store_true', help='skip the raw-scan front-end arm (e2e_raw_scans)')
+    ap.add_argument('--raw-points', type=int, default=120000, help='mean points of a raw scan (KITTI HDL-64: ~120 k)')
     ap.add_argument('--cpu-pairs', type=int, default=8, help='pairs of the bounded CPU sample')
     return ap.parse_args()
 
@@ -266,6 +268,49 @@ def run_native(args, rank, world, local_rank):
            'h2d_bytes_per_step': pipe.h2d_bytes // args.steps, 'd2h_bytes_per_step': pipe.d2h_bytes // args.steps,
            'ms_per_step': ms_e2e / args.steps, 'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches)'}
 
+    # ---- raw-scan arm: what the reference's inference loop does before its batch copy -- every
+    # 2nd point, range filter, random subsample to N points, per scan in numpy on the host (transforms/build.py:37-39)
+    # -- moved behind the H2D copy: raw ~120 k-point scans (ragged) in pinned memory -> H2D -> dclr_filter_clouds ->
+    # dclr_subsample_clouds -> forward -> D2H poses, double-buffered (deepclr_b200.models.RawScanPipeline).
+    e2e_raw = None
+    if args.kind == 'kitti' and not args.no_raw_scans and not args.no_latency:
+        from deepclr_b200 import synth
+        from deepclr_b200.models import RawScanPipeline
+        rng = np.random.Generator(np.random.PCG64(4321 + rank))
+        raw = []
+        for _ in range(2):
+            lengths = rng.integers(int(args.raw_points * 0.95), int(args.raw_points * 1.05), 2 * B).tolist()
+            stage = torch.empty((sum(lengths), 4), dtype=torch.float32).pin_memory()
+            pos = 0
+            for n in lengths:
+                xyz, inten = synth._lidar_scan(rng, n)
+                stage[pos:pos + n, :3] = torch.from_numpy(xyz.astype(np.float32))
+                stage[pos:pos + n, 3] = torch.from_numpy(inten.astype(np.float32))
+                pos += n
+            raw.append((stage, lengths))
+        rpipe = RawScanPipeline(model, args.points, nth=2, start=0, min_range=2.0, max_range=80.0, seed=7)
+        rpipe.run_all(raw[i % 2] for i in range(3))
+        rpipe.h2d_bytes = rpipe.d2h_bytes = 0
+        raw_steps = max(4, args.steps // 2)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        r0.record()
+        raw_out = rpipe.run_all(raw[i % 2] for i in range(raw_steps))
+        r1.record()
+        barrier()
+        t = torch.tensor([r0.elapsed_time(r1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        assert len(raw_out) == raw_steps and all(torch.isfinite(o).all() for o in raw_out)
+        ms_raw = float(t.item())
+        e2e_raw = {'value': world * B * raw_steps / (ms_raw * 1e-3), 'unit': 'pairs/s', 'steps': raw_steps,
+                   'ms_per_step': ms_raw / raw_steps, 'h2d_bytes_per_step': rpipe.h2d_bytes // raw_steps,
+                   'd2h_bytes_per_step': rpipe.d2h_bytes // raw_steps,
+                   'h2d_gbps': rpipe.h2d_bytes / raw_steps / (ms_raw / raw_steps) / 1e6,
+                   'front_end': 'every 2nd point -> range [2, 80] m -> random subsample to %d points, on the device' % args.points,
+                   'api': 'deepclr_b200.models.RawScanPipeline.run_all (pinned raw scans, ~%d points each)' % args.raw_points}
+        del raw, rpipe
+
     # ---- batch-1 latency (BASELINE.json configs[1]): p50 of single-pair forwards, CUDA events per call
     lat = []
     one = [r[[0, B]].contiguous() for r in resident]
@@ -316,6 +361,8 @@ def run_native(args, rank, world, local_rank):
             'stage_ms': per_call,
             'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat)},
             'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
+    if e2e_raw is not None:
+        line['e2e_raw_scans'] = e2e_raw
     if not args.no_cpu_baseline:
         v, cores, dt = cpu_oracle_pairs_per_s(args.kind, args.points, args.cpu_pairs)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',

@@ -21,9 +21,14 @@
 namespace dclr {
 
 constexpr int FLT_THREADS = 256;
-constexpr int FLT_ROWS = 8;
+#ifndef DCLR_FLT_ROWS
+#define DCLR_FLT_ROWS 8
+#endif
+constexpr int FLT_ROWS = DCLR_FLT_ROWS;            // rows of 256 points per tile, read 8 at a time
+static_assert(FLT_ROWS % 8 == 0 && FLT_ROWS <= 32, "tile height: a multiple of 8 rows, at most 32");
 constexpr int FLT_TILE = FLT_THREADS * FLT_ROWS;   // 2048 points = 32 KB of float4
 constexpr int FLT_SEGS = FLT_ROWS * (FLT_THREADS / 32);
+constexpr int FLT_PER_LANE = FLT_SEGS / 32;
 
 struct FilterArgs {
     int nth, start;          // keep i iff i >= start && (i - start) % nth == 0
@@ -55,125 +60,155 @@ __device__ __forceinline__ void st_chain(unsigned long long *p, unsigned long lo
 // cloud up to and including this tile), the number of points in the low half.
 constexpr unsigned long long ST_AGG = 1ull << 32, ST_PREFIX = 2ull << 32;
 
-// grid (max_tiles, B).  VEC4: C_in == C_out == 4, rows are float4.
+// grid (max_tiles, B), one tile per CTA.  Tiles are handed out by a per-cloud ticket, not by blockIdx: every tile a CTA
+// looks back at was taken earlier, i.e. by a CTA that is running or done, so the waits in the look-back cannot starve
+// whatever order the CTAs are scheduled in.  VEC4: C_in == C_out == 4, rows are float4.
+// (Tried: persistent CTAs drawing (cloud, tile) pairs from ONE global counter, the next ticket prefetched at the start of
+// the current tile -- 0.79 ms instead of 0.099 per 128 scans, time growing with the number of resident CTAs.)
+#ifndef DCLR_FLT_MINB
+#define DCLR_FLT_MINB 8
+#endif
+#ifndef DCLR_FLT_PREFETCH
+#define DCLR_FLT_PREFETCH 1
+#endif
 template <bool VEC4>
-__global__ void __launch_bounds__(FLT_THREADS)
-filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ offsets, int C_in, int C_out,
+__global__ void __launch_bounds__(FLT_THREADS, DCLR_FLT_MINB)
+filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ offsets, int B, int C_in, int C_out,
                      FilterArgs f, float *__restrict__ out, int32_t *__restrict__ counts,
                      unsigned *__restrict__ ticket, unsigned long long *__restrict__ status, int max_tiles) {
     __shared__ int s_seg[FLT_SEGS];
     __shared__ unsigned s_ticket;
     __shared__ int s_base;
+    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
     const int b = blockIdx.y;
     const int row0 = offsets[b];
     const int n = offsets[b + 1] - row0;
     const int ntiles = (n + FLT_TILE - 1) / FLT_TILE;
-    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-    // tiles are handed out by ticket, not by blockIdx: every tile a CTA looks back at has been taken by a CTA that is
-    // already running (or done), so the waits below cannot starve whatever order the CTAs are scheduled in
     if (threadIdx.x == 0) s_ticket = atomicAdd(&ticket[b], 1u);
     __syncthreads();
     const unsigned t = s_ticket;
-    if (ntiles > max_tiles) {                            // cloud longer than the caller's max_points: reported, not run
-        if (t == 0 && threadIdx.x == 0) counts[b] = -1;
-        return;
-    }
-    if ((int)t >= ntiles) {
-        if (t == 0 && threadIdx.x == 0) counts[b] = 0;   // empty cloud
-        return;
-    }
-    unsigned long long *st = status + (size_t)b * max_tiles;
-    const int i0 = (int)t * FLT_TILE + (int)threadIdx.x;
+    {
+        if (ntiles > max_tiles || (int)t >= ntiles) {
+            // cloud longer than the caller's max_points: reported, not run; empty cloud: count 0
+            if (t == 0 && threadIdx.x == 0 && (ntiles > max_tiles || ntiles == 0)) counts[b] = ntiles ? -1 : 0;
+            return;
+        }
+        unsigned long long *st = status + (size_t)b * max_tiles;
+        const int i0 = (int)t * FLT_TILE + (int)threadIdx.x;
+#if DCLR_FLT_PREFETCH
+        {
+            // the whole tile is requested from DRAM at once (fire-and-forget L2 prefetches, one per 128-byte line, no
+            // registers held); the row loads below then find their sectors in L2
+            const char *tile = reinterpret_cast<const char *>(pts + ((size_t)row0 + (size_t)t * FLT_TILE) * C_in);
+            const size_t rows_here = (size_t)min(FLT_TILE, n - (int)t * FLT_TILE);
+            const size_t bytes = rows_here * C_in * sizeof(float);
+            for (size_t o = (size_t)threadIdx.x * 128; o < bytes; o += (size_t)FLT_THREADS * 128)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + o));
+        }
+#endif
 
-    float4 v[FLT_ROWS];
-    unsigned keep_bits = 0, rank_bits[2] = {0, 0};   // 8 ranks of 5 bits + the keep flag each
+        // phase 1 reads only x, y (the sectors arrive whole and stay in L1 / L2); the surviving rows are read again in
+        // phase 3.  Holding the float4 rows instead costs 64 registers = 4 CTAs per SM, and the CTAs that sit in their
+        // look-back then leave the memory system idle (measured: 0.126 vs 0.099 ms per 128 scans).
+        unsigned keep_bits = 0, rank_bits[FLT_ROWS / 4];   // per row: the keep flag, the rank inside its warp (8 bits)
 #pragma unroll
-    for (int r = 0; r < FLT_ROWS; ++r) {
-        const int i = i0 + r * FLT_THREADS;
-        if (VEC4 && i < n) v[r] = __ldcs(reinterpret_cast<const float4 *>(pts) + (size_t)(row0 + i));
-    }
+        for (int q = 0; q < FLT_ROWS / 4; ++q) rank_bits[q] = 0;
 #pragma unroll
-    for (int r = 0; r < FLT_ROWS; ++r) {
-        const int i = i0 + r * FLT_THREADS;
-        bool k = false;
-        if (i < n) {
-            if (VEC4) {
-                k = keep_point(i, v[r].x, v[r].y, f);
-            } else {
-                const float *p = pts + (size_t)(row0 + i) * C_in;
-                k = keep_point(i, __ldg(p), __ldg(p + 1), f);
-            }
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, k);
-        if (lane == 0) s_seg[r * (FLT_THREADS / 32) + warp] = __popc(bal);
-        const unsigned rk = __popc(bal & ((1u << lane) - 1u));
-        keep_bits |= (k ? 1u : 0u) << r;
-        rank_bits[r >> 2] |= rk << ((r & 3) * 8);
-    }
-    __syncthreads();
-    if (warp == 0) {
-        // exclusive scan of the 64 segment counts (row-major: all warps of row 0, then row 1 ...), 2 per lane
-        const int a = s_seg[2 * lane], c = s_seg[2 * lane + 1];
-        int incl = a + c;
+        for (int r0 = 0; r0 < FLT_ROWS; r0 += 8) {
+            float2 xy[8];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, incl, d);
-            if ((int)lane >= d) incl += o;
-        }
-        const int excl = incl - (a + c);
-        s_seg[2 * lane] = excl;
-        s_seg[2 * lane + 1] = excl + a;
-        const unsigned total = (unsigned)__shfl_sync(0xffffffffu, incl, 31);
-        // decoupled look-back over the earlier tiles of this cloud: publish the own count at once, then add up the
-        // counts of the predecessors back to the nearest one that already knows its prefix, 32 tiles per round trip
-        if (lane == 0) st_chain(st + t, (t == 0 ? ST_PREFIX : ST_AGG) | total);
-        unsigned prefix = 0;
-        if (t > 0) {
-            int look = (int)t - 1;
-            for (;;) {
-                const int idx = look - (int)lane;
-                const unsigned long long w = idx >= 0 ? ld_chain(st + idx) : ST_PREFIX;   // "tile -1": prefix 0
-                const unsigned flag = (unsigned)(w >> 32);
-                const unsigned pmask = __ballot_sync(0xffffffffu, flag == 2u);
-                const unsigned zmask = __ballot_sync(0xffffffffu, flag == 0u);
-                const int fp = pmask ? __ffs(pmask) - 1 : 32;                  // nearest tile with a prefix
-                const unsigned upto = fp >= 31 ? 0xffffffffu : ((2u << fp) - 1u);
-                if (zmask & upto) {                                            // one of the needed tiles has not published
-                    __nanosleep(20);
-                    continue;
+            for (int r = 0; r < 8; ++r) {
+                const int i = i0 + (r0 + r) * FLT_THREADS;
+                xy[r] = make_float2(0.f, 0.f);
+                if (i < n) {
+                    if (VEC4) {
+                        xy[r] = __ldg(reinterpret_cast<const float2 *>(pts + (size_t)(row0 + i) * 4));
+                    } else {
+                        const float *p = pts + (size_t)(row0 + i) * C_in;
+                        xy[r] = make_float2(__ldg(p), __ldg(p + 1));
+                    }
                 }
-                unsigned val = ((int)lane <= fp) ? (unsigned)w : 0u;
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-                prefix += val;
-                if (fp < 32) break;
-                look -= 32;
             }
-            if (lane == 0) st_chain(st + t, ST_PREFIX | (unsigned long long)(prefix + total));
-        }
-        if (lane == 0) {
-            s_base = (int)prefix;
-            if ((int)t == ntiles - 1) counts[b] = (int)(prefix + total);
-        }
-    }
-    __syncthreads();
-    const int base = s_base;
 #pragma unroll
-    for (int r = 0; r < FLT_ROWS; ++r) {
-        if (!((keep_bits >> r) & 1u)) continue;
-        const int rk = (rank_bits[r >> 2] >> ((r & 3) * 8)) & 0xff;
-        const size_t dst = (size_t)row0 + base + s_seg[r * (FLT_THREADS / 32) + warp] + rk;
-        if (VEC4) {
-            reinterpret_cast<float4 *>(out)[dst] = v[r];
-        } else {
-            const float *p = pts + (size_t)(row0 + i0 + r * FLT_THREADS) * C_in;
-            for (int c = 0; c < C_out; ++c) out[dst * C_out + c] = __ldg(p + c);
+            for (int r = 0; r < 8; ++r) {
+                const int i = i0 + (r0 + r) * FLT_THREADS;
+                const bool k = (i < n) && keep_point(i, xy[r].x, xy[r].y, f);
+                const unsigned bal = __ballot_sync(0xffffffffu, k);
+                if (lane == 0) s_seg[(r0 + r) * (FLT_THREADS / 32) + warp] = __popc(bal);
+                const unsigned rk = __popc(bal & ((1u << lane) - 1u));
+                keep_bits |= (k ? 1u : 0u) << (r0 + r);
+                rank_bits[(r0 + r) >> 2] |= rk << (((r0 + r) & 3) * 8);
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {
+            // exclusive scan of the segment counts (row-major: all warps of row 0, then row 1 ...), FLT_PER_LANE per lane
+            int c[FLT_PER_LANE], sum = 0;
+#pragma unroll
+            for (int q = 0; q < FLT_PER_LANE; ++q) { c[q] = s_seg[FLT_PER_LANE * lane + q]; sum += c[q]; }
+            int incl = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)lane >= d) incl += o;
+            }
+            int run = incl - sum;
+#pragma unroll
+            for (int q = 0; q < FLT_PER_LANE; ++q) { s_seg[FLT_PER_LANE * lane + q] = run; run += c[q]; }
+            const unsigned total = (unsigned)__shfl_sync(0xffffffffu, incl, 31);
+            // decoupled look-back over the earlier tiles of this cloud: publish the own count at once, then add up the
+            // counts of the predecessors back to the nearest one that already knows its prefix, 32 tiles per round trip
+            if (lane == 0) st_chain(st + t, (t == 0 ? ST_PREFIX : ST_AGG) | total);
+            unsigned prefix = 0;
+            if (t > 0) {
+                int look = (int)t - 1;
+                for (;;) {
+                    const int idx = look - (int)lane;
+                    const unsigned long long w = idx >= 0 ? ld_chain(st + idx) : ST_PREFIX;   // "tile -1": prefix 0
+                    const unsigned flag = (unsigned)(w >> 32);
+                    const unsigned pmask = __ballot_sync(0xffffffffu, flag == 2u);
+                    const unsigned zmask = __ballot_sync(0xffffffffu, flag == 0u);
+                    const int fp = pmask ? __ffs(pmask) - 1 : 32;                  // nearest tile with a prefix
+                    const unsigned upto = fp >= 31 ? 0xffffffffu : ((2u << fp) - 1u);
+                    if (zmask & upto) {                                            // a needed tile has not published yet
+                        __nanosleep(20);
+                        continue;
+                    }
+                    unsigned val = ((int)lane <= fp) ? (unsigned)w : 0u;
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+                    prefix += val;
+                    if (fp < 32) break;
+                    look -= 32;
+                }
+                if (lane == 0) st_chain(st + t, ST_PREFIX | (unsigned long long)(prefix + total));
+            }
+            if (lane == 0) {
+                s_base = (int)prefix;
+                if ((int)t == ntiles - 1) counts[b] = (int)(prefix + total);
+            }
+        }
+        __syncthreads();
+        const int base = s_base;
+#pragma unroll
+        for (int r = 0; r < FLT_ROWS; ++r) {
+            if (!((keep_bits >> r) & 1u)) continue;
+            const int rk = (rank_bits[r >> 2] >> ((r & 3) * 8)) & 0xff;
+            const size_t dst = (size_t)row0 + base + s_seg[r * (FLT_THREADS / 32) + warp] + rk;
+            if (VEC4) {
+                __stcs(reinterpret_cast<float4 *>(out) + dst,
+                       __ldg(reinterpret_cast<const float4 *>(pts) + (size_t)(row0 + i0 + r * FLT_THREADS)));
+            } else {
+                const float *p = pts + (size_t)(row0 + i0 + r * FLT_THREADS) * C_in;
+                for (int c = 0; c < C_out; ++c) out[dst * C_out + c] = __ldg(p + c);
+            }
         }
     }
 }
 
-// ---- keyed permutation of [0, n): balanced Feistel network on an even number of bits >= log2 n, cycle walking back
-// into the domain (expected < 4 walks).  A bijection by construction, so the first N values are N distinct rows.
+// ---- keyed permutation of [0, n): 4-round Feistel network on ceil(log2 n) bits, cycle walking back into the domain
+// (first version: 6 rounds on an even bit count, up to 4 walks + an integer division per row -- the kernel was bound by
+// the integer pipe, 0.072 ms per 128 x 16384 rows).  A bijection by construction, so the first N values are N distinct rows.
 __device__ __forceinline__ unsigned mix32(unsigned x) {
     x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
     return x;
@@ -181,21 +216,23 @@ __device__ __forceinline__ unsigned mix32(unsigned x) {
 __device__ __forceinline__ unsigned feistel_perm(unsigned j, unsigned n, unsigned key) {
     if (n <= 1) return 0;
     int bits = 32 - __clz(n - 1);
-    bits = (bits + 1) & ~1;
     if (bits < 2) bits = 2;
-    const int half = bits >> 1;
-    const unsigned mask = (1u << half) - 1u;
+    // L = the high `ha` bits, R = the low `hb` bits, ha >= hb (unbalanced for an odd bit count: the domain stays
+    // below 2n, < 2 walks on average); a round maps (L, R) -> (R, L ^ F(R)) and swaps the two widths, an even number
+    // of rounds restores them
+    const int hb = bits >> 1, ha = bits - hb;
+    const unsigned ma = (1u << ha) - 1u, mb = (1u << hb) - 1u;
     unsigned x = j;
     do {
-        unsigned L = x >> half, R = x & mask;
+        unsigned L = x >> hb, R = x & mb;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-            const unsigned F = mix32(R ^ (key + 0x9e3779b9u * (unsigned)(r + 1))) & mask;
+        for (int r = 0; r < 4; ++r) {
+            const unsigned F = mix32(R ^ (key + 0x9e3779b9u * (unsigned)(r + 1))) & ((r & 1) ? mb : ma);
             const unsigned nl = R;
             R = L ^ F;
             L = nl;
         }
-        x = (L << half) | R;
+        x = (L << hb) | R;
     } while (x >= n);
     return x;
 }
@@ -221,7 +258,7 @@ subsample_clouds_kernel(const float *__restrict__ in, const int32_t *__restrict_
     for (int r = 0; r < SUB_ROWS; ++r) {
         const int j = j0 + r * 256;
         src[r] = -1;
-        if (j < N_out && n > 0) src[r] = ordered ? j : (int)feistel_perm((unsigned)(j % n), (unsigned)n, key);
+        if (j < N_out && n > 0) src[r] = ordered ? j : (int)feistel_perm((unsigned)(j < n ? j : j % n), (unsigned)n, key);
         v[r] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (VEC4 && src[r] >= 0) v[r] = __ldg(reinterpret_cast<const float4 *>(in) + (size_t)(row0 + src[r]));
     }
@@ -270,8 +307,8 @@ extern "C" int dclr_filter_clouds(const float *pts, const int32_t *offsets, int 
     auto *ticket = (unsigned *)((char *)ws + chain_bytes);
     dim3 grid(tiles, B);
     const bool vec4 = C_in == 4 && C_out == 4 && ((uintptr_t)pts % 16 == 0) && ((uintptr_t)out % 16 == 0);
-    if (vec4) filter_clouds_kernel<true><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, C_in, C_out, f, out, counts_out, ticket, chain, tiles);
-    else filter_clouds_kernel<false><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, C_in, C_out, f, out, counts_out, ticket, chain, tiles);
+    if (vec4) filter_clouds_kernel<true><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, B, C_in, C_out, f, out, counts_out, ticket, chain, tiles);
+    else filter_clouds_kernel<false><<<grid, FLT_THREADS, 0, st>>>(pts, offsets, B, C_in, C_out, f, out, counts_out, ticket, chain, tiles);
     e = cudaGetLastError();
     scratch_free(ws, st);
     if (e != cudaSuccess) return fail(DCLR_E_CUDA, "launch of filter_clouds_kernel failed: %s", cudaGetErrorString(e));

@@ -46,6 +46,9 @@ class HostPipeline:
         self._used[slot] = True
         self.h2d_bytes += host.numel() * host.element_size()
 
+    def _forward(self, slot: int) -> torch.Tensor:
+        return self.model(self._in[slot])[0]
+
     def run(self, batches: Iterable[torch.Tensor]) -> Iterator[torch.Tensor]:
         it = iter(batches)
         nxt = next(it, None)
@@ -60,7 +63,7 @@ class HostPipeline:
                 self._stage((i + 1) % self.depth, nxt)
             main.wait_event(self._loaded[slot])
             with torch.no_grad():
-                y = self.model(self._in[slot])[0]
+                y = self._forward(slot)
             self._freed[slot].record(main)
             o = i % (self.depth + 1)
             if self._out[o] is None or self._out[o].shape != y.shape:
@@ -88,3 +91,57 @@ class HostPipeline:
     def synchronize(self) -> None:
         self._copy.synchronize()
         torch.cuda.current_stream(self.device).synchronize()
+
+
+class RawScanPipeline(HostPipeline):
+    """The same double-buffered pipeline fed with RAW scans of different lengths: `batches` yields
+    `(stage, lengths)` -- stage = [total, C] float32 host tensor (pinned: deepclr_b200.data.datasets.stage_scans) with
+    the 2B scans of B pairs back to back, templates first (deepclr/data/build.py:82), lengths = rows per scan.
+    Per batch: one H2D copy of the raw bytes, then on the device SystematicErasing -> RangeSelection ->
+    TruncateDimension (dclr_filter_clouds), the size-equalising random subsample to `n_points` rows per cloud
+    (dclr_subsample_clouds) and the forward -- what the reference does per cloud in numpy on the host before its
+    batch copy (deepclr/data/transforms/build.py:37-39, deepclr/models/base.py:130-135)."""
+
+    def __init__(self, model, n_points: int, nth: int = 1, start: int = 0, min_range: float = 0.0,
+                 max_range: float = float('inf'), seed: int = 0, depth: int = 2,
+                 device: Optional[torch.device] = None):
+        super().__init__(model, depth, device)
+        self.n_points, self.seed = int(n_points), int(seed)
+        self.filter_args = dict(nth=int(nth), start=int(start), min_range=float(min_range), max_range=float(max_range))
+        self._meta: List[Optional[tuple]] = [None] * self.depth
+        self._batch_no = 0
+
+    def _stage(self, slot: int, item) -> None:
+        stage, lengths = item
+        total, C = int(stage.shape[0]), int(stage.shape[1])
+        if total != sum(lengths):
+            raise ValueError('stage rows != sum(lengths)')
+        buf = self._in[slot]
+        if buf is None or buf[0].shape[0] < total or buf[0].shape[1] != C or buf[1].shape[0] < len(lengths) + 1:
+            cap = int(total * 1.25) + 1
+            buf = self._in[slot] = (torch.empty((cap, C), dtype=torch.float32, device=self.device),
+                                    torch.empty(len(lengths) + 1, dtype=torch.int32, device=self.device))
+            self._used[slot] = False
+        with torch.cuda.stream(self._copy):
+            if self._used[slot]:
+                self._copy.wait_event(self._freed[slot])
+            # a fresh pinned block per batch: torch's caching host allocator hands it out again only after this copy
+            off = torch.empty(len(lengths) + 1, dtype=torch.int32, pin_memory=True)
+            off[0] = 0
+            off[1:] = torch.cumsum(torch.tensor(lengths, dtype=torch.int64), 0).to(torch.int32)
+            buf[0][:total].copy_(stage, non_blocking=True)
+            buf[1][:len(lengths) + 1].copy_(off[:len(lengths) + 1], non_blocking=True)
+            self._loaded[slot].record(self._copy)
+        self._used[slot] = True
+        self._meta[slot] = (total, list(lengths))
+        self.h2d_bytes += total * C * 4 + (len(lengths) + 1) * 4
+
+    def _forward(self, slot: int) -> torch.Tensor:
+        from ..data import device as dev_ops
+        total, lengths = self._meta[slot]
+        pts, off = self._in[slot]
+        rc = dev_ops.RaggedClouds(pts[:total], off[:len(lengths) + 1], lengths)
+        rc = dev_ops.filter_clouds(rc, out_dim=self.model.get_input_dim(), **self.filter_args)
+        x = dev_ops.subsample_clouds(rc, self.n_points, seed=self.seed + self._batch_no)
+        self._batch_no += 1
+        return self.model(x)[0]

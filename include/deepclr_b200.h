@@ -193,7 +193,7 @@ int dclr_filter_clouds(const float *pts, const int32_t *offsets, int B, int max_
  * x_out [B, N_out, C_out] -- ModelInferenceHelper.stack (deepclr/models/base.py:130-135: cloud[randperm(n)[:N_out]])
  * and RandomErasing(max_points) (transforms.py:128-131), batched.  Cloud b = rows offsets[b] .. + n_b with
  * n_b = counts[b] (counts = NULL: offsets[b+1] - offsets[b]).  Row j of cloud b is source row P_b(j), P_b a keyed
- * bijection of [0, n_b) (6-round balanced Feistel network + cycle walking; key from seed and b), so the rows are
+ * bijection of [0, n_b) (4-round Feistel network on ceil(log2 n_b) bits + cycle walking; key from seed and b), so the rows are
  * distinct; n_b == N_out with ordered_if_equal != 0 copies the cloud in order (the reference does not permute equal
  * sizes).  n_b < N_out: rows j >= n_b repeat P_b(j mod n_b) and *short_out (optional, DEVICE i32) counts such clouds;
  * n_b == 0 gives zeros and perm -1.  perm_out (optional) [B, N_out] i32 = the chosen source rows. */

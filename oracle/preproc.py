@@ -55,20 +55,52 @@ def cloud_key(seed: int, b: int) -> int:
 def feistel_perm(j: int, n: int, key: int) -> int:
     if n <= 1:
         return 0
-    bits = (n - 1).bit_length()
-    bits = (bits + 1) & ~1
-    bits = max(bits, 2)
-    half = bits >> 1
-    mask = (1 << half) - 1
+    bits = max((n - 1).bit_length(), 2)
+    hb = bits >> 1
+    ha = bits - hb
+    ma, mb = (1 << ha) - 1, (1 << hb) - 1
     x = j
     while True:
-        L, R = x >> half, x & mask
-        for r in range(6):
-            F = _mix32(R ^ ((key + 0x9e3779b9 * (r + 1)) & M32)) & mask
+        L, R = x >> hb, x & mb
+        for r in range(4):
+            F = _mix32(R ^ ((key + 0x9e3779b9 * (r + 1)) & M32)) & (mb if r & 1 else ma)
             L, R = R, L ^ F
-        x = (L << half) | R
+        x = (L << hb) | R
         if x < n:
             return x
+
+
+def _mix32_np(x):
+    x = x & M32
+    x ^= x >> 16
+    x = (x * 0x7feb352d) & M32
+    x ^= x >> 15
+    x = (x * 0x846ca68b) & M32
+    x ^= x >> 16
+    return x
+
+
+def feistel_perm_np(j: np.ndarray, n: int, key: int) -> np.ndarray:
+    """Vectorised feistel_perm (uint64 arithmetic) for full-size checks."""
+    j = np.asarray(j, dtype=np.uint64)
+    if n <= 1:
+        return np.zeros(j.shape, np.int64)
+    bits = max((n - 1).bit_length(), 2)
+    hb = bits >> 1
+    ha = bits - hb
+    ma, mb = np.uint64((1 << ha) - 1), np.uint64((1 << hb) - 1)
+    x = j.copy()
+    todo = np.ones(x.shape, bool)
+    while todo.any():
+        cur = x[todo]
+        L, R = cur >> np.uint64(hb), cur & mb
+        for r in range(4):
+            F = _mix32_np(R ^ np.uint64((key + 0x9e3779b9 * (r + 1)) & M32)) & (mb if r & 1 else ma)
+            L, R = R, L ^ F
+        cur = (L << np.uint64(hb)) | R
+        x[todo] = cur
+        todo[todo] = cur >= n
+    return x.astype(np.int64)
 
 
 def subsample_rows(n: int, n_out: int, seed: int, b: int, ordered_if_equal: bool = True) -> np.ndarray:
@@ -77,4 +109,4 @@ def subsample_rows(n: int, n_out: int, seed: int, b: int, ordered_if_equal: bool
     if n == n_out and ordered_if_equal:
         return np.arange(n_out, dtype=np.int32)
     key = cloud_key(seed, b)
-    return np.array([feistel_perm(j % n, n, key) for j in range(n_out)], np.int32)
+    return feistel_perm_np(np.arange(n_out) % n, n, key).astype(np.int32)

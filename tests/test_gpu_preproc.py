@@ -159,3 +159,31 @@ def test_stack_on_device_equalises_sizes():
     assert x.shape == (2, 900, 4) and torch.equal(x[0], t)
     got = {tuple(r) for r in x[1].cpu().numpy().tolist()}
     assert len(got) == 900 and got <= {tuple(r) for r in s.cpu().numpy().tolist()}
+
+
+def test_raw_scan_pipeline_equals_prepare_then_forward(dev_ops):
+    """RawScanPipeline (H2D of raw ragged scans -> filter -> subsample -> forward, double-buffered) gives the poses of
+    the same steps done one by one."""
+    from deepclr_b200.models import RawScanPipeline
+    from tests.util import build_from_golden
+    g = load_golden('kitti_small_b2')
+    model, cfg = build_from_golden(g, DEV)
+    N = int(g['n'])
+    rng = np.random.Generator(np.random.PCG64(31))
+    batches = []
+    for _ in range(5):
+        lengths = rng.integers(3 * N, 4 * N, 4).tolist()
+        scans = [np.concatenate([rng.uniform(-40, 40, (n, 2)), rng.uniform(-2, 1, (n, 1)), rng.uniform(0, 1, (n, 1))],
+                                1).astype(np.float32) for n in lengths]
+        batches.append((torch.from_numpy(np.concatenate(scans)).pin_memory(), lengths, scans))
+    pipe = RawScanPipeline(model, N, nth=2, start=0, min_range=1.0, max_range=39.0, seed=100)
+    ys = pipe.run_all((b[0], b[1]) for b in batches)
+    assert len(ys) == 5
+    for i, (stage, lengths, scans) in enumerate(batches):
+        rc = dev_ops.filter_clouds(dev_ops.RaggedClouds.from_list(scans, DEV), 2, 0, 1.0, 39.0, out_dim=4)
+        assert int(rc.counts.min()) >= N
+        x = dev_ops.subsample_clouds(rc, N, seed=100 + i)
+        with torch.no_grad():
+            y = model(x)[0]
+        assert torch.equal(ys[i], y.cpu()), i
+    assert pipe.h2d_bytes == sum(b[0].numel() * 4 + 5 * 4 for b in batches)

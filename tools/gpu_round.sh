@@ -20,3 +20,10 @@ for k in ${NCU_KERNELS:-fps_bucket_kernel}; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 6 -c 1 -f -o gpurun_out/full_$k \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/ncu_full_$k.log 2>&1; echo "ncu full $k rc=$?"
 done
+# pre-processing kernels: op bench + ncu --set full of both
+timeout 300 python tools/preproc_bench.py > gpurun_out/preproc.jsonl 2> gpurun_out/preproc.err; echo "preproc bench rc=$?"
+cat gpurun_out/preproc.jsonl
+for k in filter_clouds_kernel subsample_clouds_kernel; do
+  timeout 300 ncu --set full --clock-control none --import-source on -k regex:$k -s 4 -c 1 -f -o gpurun_out/full_$k \
+    python tools/preproc_bench.py --iters 2 > gpurun_out/ncu_full_$k.log 2>&1; echo "ncu full $k rc=$?"
+done
