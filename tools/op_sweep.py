@@ -39,7 +39,7 @@ def main():
     ap.add_argument('--sizes', default='1024,2048,4096,8192,16384,32768,65536,131072')
     ap.add_argument('--clouds', type=int, default=8)
     ap.add_argument('--iters', type=int, default=10)
-    ap.add_argument('--ops', default='fps,ball,knn')
+    ap.add_argument('--ops', default='fps,ball,knn,sa')
     ap.add_argument('--no-ref', action='store_true')
     args = ap.parse_args()
     from deepclr_b200 import synth
@@ -111,7 +111,74 @@ def main():
                     line.update(standin_ms=rms, speedup_vs_standin=rms / ms, index_agreement_with_standin=same,
                                 note='stand-in = torch.cdist^2 + topk (torch_cluster absent); cdist rounds differently')
                 print(json.dumps(line), flush=True)
+        if 'sa' in ops and N <= 65536:
+            try:
+                # fused gather -> shared MLP -> ReLU -> max-pool (SURVEY a4+a5, both scales of the KITTI config) vs the
+                # reference composition on the same neighbour lists: grouping_operation (reference kernel) + 3 x (1x1 conv
+                # + ReLU) through torch / cuDNN fp32 (TF32 off) + max_pool2d (pointnet2_modules.py:40-52)
+                import yaml
+                from deepclr_b200.config.config import Config
+                from deepclr_b200.data.labels import LabelType
+                from deepclr_b200.models.build import ModelType, build_model
+                cfg = yaml.safe_load(open(os.path.join(ROOT, 'configs', 'kitti_model.yaml')))
+                sa = cfg['params']['cloud_features']['params']
+                sa['npoint'] = [M]
+                c = Config._from_dict(cfg)
+                c.label_type = LabelType.create(c.label_type)
+                c.model_type = ModelType.create(c.model_type)
+                torch.manual_seed(0)
+                model = build_model(c).eval().to(dev)
+                model.numerics = 'fp32'
+                x4 = torch.from_numpy(np.stack([synth.kitti_pair(100 + i, N)[0] for i in range(B)]).astype(np.float32)).to(dev)
+                with torch.no_grad():
+                    feat = model.cloud_features(x4)
+                    native = model._native
+                    native.set_timing(True)
+                    for _ in range(args.iters):
+                        model.cloud_features(x4)
+                    torch.cuda.synchronize()
+                    stage_ms, calls = native.collect_timing()
+                    native.set_timing(False)
+                ms = stage_ms.get('sa_mlp_maxpool', 0.0) / max(calls, 1)
+                radii, nss = sa['radii'][0], sa['nsamples'][0]
+                flops = 2.0 * B * M * sum(ns * (4 * 16 + 16 * 16 + 16 * 32) for ns in nss)
+                line = {'op': 'sa_mlp_maxpool', 'N': N, 'npoint': M, 'clouds': B, 'nsamples': nss, 'ms': ms,
+                        'dense_equiv_TFLOPs': flops / ms / 1e9 if ms > 0 else None,
+                        'note': 'fused kernel skips padded duplicate rows exactly; dense-equivalent flops as the reference computes them'}
+                if have_ref:
+                    old_tf32 = torch.backends.cudnn.allow_tf32
+                    torch.backends.cudnn.allow_tf32 = False
+                    sd = model.state_dict()
+                    xyz3 = x4[:, :, :3].contiguous()
+                    xyz_f = xyz3.transpose(1, 2).contiguous()
+                    feats = x4[:, :, 3:].transpose(1, 2).contiguous()
+                    new_xyz = feat[:, :3, :].transpose(1, 2).contiguous()
+                    idxs = [ref_cuda.ball_query(r, ns, xyz3, new_xyz) for r, ns in zip(radii, nss)]
 
+                    def ref_sa():
+                        outs = []
+                        for s_, idx in enumerate(idxs):
+                            g = ref_cuda.grouping_operation(xyz_f, idx) - new_xyz.transpose(1, 2).unsqueeze(-1)
+                            g = torch.cat([g, ref_cuda.grouping_operation(feats, idx)], dim=1)
+                            for layer in range(3):
+                                g = ref_cuda._pointwise(g, sd[f'_cloud_layers.0._sa0.mlps.{s_}.layer{layer}.conv.weight'],
+                                                        sd[f'_cloud_layers.0._sa0.mlps.{s_}.layer{layer}.conv.bias'])
+                            outs.append(torch.nn.functional.max_pool2d(g, kernel_size=[1, g.size(3)]).squeeze(-1))
+                        return torch.cat(outs, dim=1)
+                    with torch.no_grad():
+                        rms = timed(ref_sa, 3, warm=1)
+                        ref = ref_sa()
+                    err = float((feat[:, 3:, :] - ref).abs().max().item())
+                    line.update(ref_ms=rms, speedup=rms / ms if ms > 0 else None, max_abs_err=err,
+                                ref_max_abs=float(ref.abs().max().item()))
+                    torch.backends.cudnn.allow_tf32 = old_tf32
+                    del ref, idxs
+                del model, feat
+                torch.cuda.empty_cache()
+                print(json.dumps(line), flush=True)
+
+            except Exception as e:       # a shape the model handle does not take: reported, the sweep goes on
+                print(json.dumps({'op': 'sa_mlp_maxpool', 'N': N, 'error': str(e)[:300]}), flush=True)
 
 if __name__ == '__main__':
     main()
