@@ -63,8 +63,11 @@ constexpr unsigned long long ST_AGG = 1ull << 32, ST_PREFIX = 2ull << 32;
 // grid (max_tiles, B), one tile per CTA.  Tiles are handed out by a per-cloud ticket, not by blockIdx: every tile a CTA
 // looks back at was taken earlier, i.e. by a CTA that is running or done, so the waits in the look-back cannot starve
 // whatever order the CTAs are scheduled in.  VEC4: C_in == C_out == 4, rows are float4.
-// (Tried: persistent CTAs drawing (cloud, tile) pairs from ONE global counter, the next ticket prefetched at the start of
-// the current tile -- 0.79 ms instead of 0.099 per 128 scans, time growing with the number of resident CTAs.)
+// (Tried: persistent CTAs drawing (cloud, tile) pairs from ONE global counter with the next ticket PREFETCHED at the start
+// of the current tile -- 0.79 ms instead of 0.099 per 128 scans, growing with the number of resident CTAs: a prefetched
+// ticket is a tile nobody works on yet, so a look-back can wait for a CTA that first has to finish its own tile, whose
+// look-back waits for another such CTA ...: dependency chains as long as the grid.  A ticket must be drawn at the
+// moment its tile is started.  Taller tiles (16 / 24 / 32 rows) were slower as well: 0.115 / 0.117 / 0.178 ms.)
 #ifndef DCLR_FLT_MINB
 #define DCLR_FLT_MINB 8
 #endif
@@ -85,6 +88,17 @@ filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ 
     const int n = offsets[b + 1] - row0;
     const int ntiles = (n + FLT_TILE - 1) / FLT_TILE;
     if (threadIdx.x == 0) s_ticket = atomicAdd(&ticket[b], 1u);
+#if DCLR_FLT_PREFETCH
+    if ((int)blockIdx.x < ntiles && ntiles <= max_tiles) {
+        // While the ticket is on its way: request tile blockIdx.x from DRAM (fire-and-forget L2 prefetches, one per
+        // 128-byte line, no registers held).  CTAs start in blockIdx order, so the ticket is usually this very tile; if
+        // not, the tile belongs to another CTA of this launch and the prefetch serves that one.
+        const char *tile = reinterpret_cast<const char *>(pts + ((size_t)row0 + (size_t)blockIdx.x * FLT_TILE) * C_in);
+        const size_t bytes = (size_t)min(FLT_TILE, n - (int)blockIdx.x * FLT_TILE) * C_in * sizeof(float);
+        for (size_t o = (size_t)threadIdx.x * 128; o < bytes; o += (size_t)FLT_THREADS * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + o));
+    }
+#endif
     __syncthreads();
     const unsigned t = s_ticket;
     {
@@ -95,17 +109,6 @@ filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ 
         }
         unsigned long long *st = status + (size_t)b * max_tiles;
         const int i0 = (int)t * FLT_TILE + (int)threadIdx.x;
-#if DCLR_FLT_PREFETCH
-        {
-            // the whole tile is requested from DRAM at once (fire-and-forget L2 prefetches, one per 128-byte line, no
-            // registers held); the row loads below then find their sectors in L2
-            const char *tile = reinterpret_cast<const char *>(pts + ((size_t)row0 + (size_t)t * FLT_TILE) * C_in);
-            const size_t rows_here = (size_t)min(FLT_TILE, n - (int)t * FLT_TILE);
-            const size_t bytes = rows_here * C_in * sizeof(float);
-            for (size_t o = (size_t)threadIdx.x * 128; o < bytes; o += (size_t)FLT_THREADS * 128)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + o));
-        }
-#endif
 
         // phase 1 reads only x, y (the sectors arrive whole and stay in L1 / L2); the surviving rows are read again in
         // phase 3.  Holding the float4 rows instead costs 64 registers = 4 CTAs per SM, and the CTAs that sit in their
@@ -163,23 +166,23 @@ filter_clouds_kernel(const float *__restrict__ pts, const int32_t *__restrict__ 
             if (t > 0) {
                 int look = (int)t - 1;
                 for (;;) {
-                    const int idx = look - (int)lane;
-                    const unsigned long long w = idx >= 0 ? ld_chain(st + idx) : ST_PREFIX;   // "tile -1": prefix 0
-                    const unsigned flag = (unsigned)(w >> 32);
-                    const unsigned pmask = __ballot_sync(0xffffffffu, flag == 2u);
-                    const unsigned zmask = __ballot_sync(0xffffffffu, flag == 0u);
-                    const int fp = pmask ? __ffs(pmask) - 1 : 32;                  // nearest tile with a prefix
-                    const unsigned upto = fp >= 31 ? 0xffffffffu : ((2u << fp) - 1u);
-                    if (zmask & upto) {                                            // a needed tile has not published yet
+                    // 64 predecessors per round trip: lane l inspects tiles look - 2l and look - 2l - 1 ("tile -1" has
+                    // prefix 0); a KITTI scan has <= 65 tiles, so one poll usually settles it
+                    const int i0 = look - 2 * (int)lane, i1 = i0 - 1;
+                    const unsigned long long w0 = i0 >= 0 ? ld_chain(st + i0) : ST_PREFIX;
+                    const unsigned long long w1 = i1 >= 0 ? ld_chain(st + i1) : ST_PREFIX;
+                    const unsigned f0 = (unsigned)(w0 >> 32), f1 = (unsigned)(w1 >> 32);
+                    const unsigned mypos = f0 == 2u ? 2u * lane : (f1 == 2u ? 2u * lane + 1u : 64u);
+                    const unsigned fp = __reduce_min_sync(0xffffffffu, mypos);     // nearest tile with a prefix
+                    const bool bad = (2u * lane <= fp && f0 == 0u) || (2u * lane + 1u <= fp && f1 == 0u);
+                    if (__any_sync(0xffffffffu, bad)) {                            // a needed tile has not published yet
                         __nanosleep(20);
                         continue;
                     }
-                    unsigned val = ((int)lane <= fp) ? (unsigned)w : 0u;
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-                    prefix += val;
-                    if (fp < 32) break;
-                    look -= 32;
+                    const unsigned val = (2u * lane <= fp ? (unsigned)w0 : 0u) + (2u * lane + 1u <= fp ? (unsigned)w1 : 0u);
+                    prefix += __reduce_add_sync(0xffffffffu, val);
+                    if (fp < 64u) break;
+                    look -= 64;
                 }
                 if (lane == 0) st_chain(st + t, ST_PREFIX | (unsigned long long)(prefix + total));
             }
