@@ -348,6 +348,18 @@ def run_native(args, rank, world, local_rank):
     else:
         ach = bytes_stage.get(top, 0) / (per_call[top] * 1e-3) / 1e9
         roof = {'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': ach / peaks['hbm']}
+    # every stage against its own roof (the dominant one is repeated in `roofline`): tensor stages in dense-equivalent
+    # TFLOP/s vs the sustained bf16 peak, the point ops in algorithmic GB/s vs the measured HBM peak
+    roof_stages = {}
+    for k, t_ms in per_call.items():
+        if t_ms <= 0:
+            continue
+        if k in flop_stage:
+            v = B * flop_stage[k] / (t_ms * 1e-3) / 1e12
+            roof_stages[k] = {'bound': 'tensor', 'achieved': v, 'unit': 'TFLOP/s', 'frac': v / peaks['tf'], 'ms': t_ms}
+        elif k in bytes_stage:
+            v = bytes_stage[k] / (t_ms * 1e-3) / 1e9
+            roof_stages[k] = {'bound': 'hbm', 'achieved': v, 'unit': 'GB/s', 'frac': v / peaks['hbm'], 'ms': t_ms}
     roof.update({'kernel': top, 'traffic': ncu_traffic(top, args), 'peak_source': peaks['src'], 'ms_per_launch': per_call[top],
                  'share_of_step': per_call[top] / (ms / args.steps)})
 
@@ -358,7 +370,7 @@ def run_native(args, rank, world, local_rank):
                        'points_per_cloud': N, 'numerics': args.numerics, 'parallelism': f'dp{world} (independent pairs)',
                        'l2': f'{ROTATE} distinct resident input batches cycled + >126 MB of per-step workspace traffic'},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof,
-            'stage_ms': per_call,
+            'stage_ms': per_call, 'roofline_stages': roof_stages,
             'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat)},
             'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
     if e2e_raw is not None:

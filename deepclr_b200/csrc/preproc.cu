@@ -297,7 +297,7 @@ extern "C" int dclr_filter_clouds(const float *pts, const int32_t *offsets, int 
     cudaStream_t st = (cudaStream_t)stream;
     FilterArgs f;
     f.nth = nth; f.start = start; f.rmin = min_range; f.rmax = max_range;
-    f.use_range = !(min_range == 0.0f && isinf(max_range) && max_range > 0);
+    f.use_range = !(min_range == 0.0f && isinf(max_range));   // np.isinf: either sign, as the reference tests it
     // per-tile status words (8 B) + per-cloud ticket (4 B), zeroed per call
     const int tiles = max_points > 0 ? div_up(max_points, FLT_TILE) : 1;
     void *ws = nullptr;

@@ -187,3 +187,30 @@ def test_raw_scan_pipeline_equals_prepare_then_forward(dev_ops):
             y = model(x)[0]
         assert torch.equal(ys[i], y.cpu()), i
     assert pipe.h2d_bytes == sum(b[0].numel() * 4 + 5 * 4 for b in batches)
+
+
+def test_filter_random_ragged_batches(dev_ops):
+    """40 random ragged batches (empty clouds, sizes around the 2048-point tile edge, C = 3..6, random nth / start /
+    range, +-inf and NaN coordinates): rows and counts bit-equal to the restated reference transforms."""
+    rng = np.random.Generator(np.random.PCG64(2024))
+    for trial in range(40):
+        B = int(rng.integers(1, 24))
+        C = int(rng.integers(3, 7))
+        out_dim = int(rng.integers(3, C + 1))
+        sizes = [int(rng.choice([0, 1, 2047, 2048, 2049, 4096, int(rng.integers(0, 9000))])) for _ in range(B)]
+        clouds = []
+        for n in sizes:
+            c = rng.uniform(-70, 70, (n, C)).astype(np.float32)
+            if n > 10:
+                c[rng.integers(0, n, 3), rng.integers(0, 2, 3)] = [np.nan, np.inf, -np.inf]
+            clouds.append(c)
+        nth = int(rng.integers(1, 5))
+        start = int(rng.integers(0, nth))
+        rmin = float(rng.choice([0.0, 1.5, 10.0]))
+        rmax = float(rng.choice([np.inf, 45.0, 69.0]))
+        out = dev_ops.filter_clouds(dev_ops.RaggedClouds.from_list(clouds, DEV), nth, start, rmin, rmax, out_dim=out_dim)
+        counts = out.counts.cpu().numpy()
+        for b, c in enumerate(clouds):
+            want = preproc.filter_cloud(c, nth, start, rmin, rmax, out_dim)
+            assert counts[b] == want.shape[0], (trial, b)
+            assert np.array_equal(_rows(out, b), want, equal_nan=True), (trial, b)
