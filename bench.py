@@ -183,7 +183,7 @@ def run_reference(args, rank, world):
             'cpu_baseline': {'value': value, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT, flush=True)
 
 
 def run_native(args, rank, world, local_rank):
@@ -385,13 +385,27 @@ def run_native(args, rank, world, local_rank):
         v, cores, dt = cpu_oracle_pairs_per_s(args.kind, args.points, args.cpu_pairs)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
                                 'sample': f'{args.cpu_pairs} batch-1 forwards of {N}-point pairs ({dt:.1f} s)'}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+RESULT = sys.stdout
+
+
+def claim_stdout():
+    """fd 1 carries the ONE result line and nothing else: whatever a library writes to stdout from here on (NCCL prints
+    its version banner there when NCCL_DEBUG is set) is sent to stderr; the JSON line goes to the saved descriptor."""
+    global RESULT
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    RESULT = os.fdopen(real, 'w')
+
+
 def main():
     args = parse_args()
+    claim_stdout()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local_rank = int(os.environ.get('LOCAL_RANK', 0))

@@ -35,17 +35,19 @@ struct SaParams {
     float w[2][SA_WMAX];     // per scale: W1[H1*CIN] b1[H1] W2[H2*H1] b2[H2] W3[H3*H2] b3[H3]
 };
 
-template <int CIN, int H1, int H2, int H3>
+// CPW = centres per warp: 32 for full batches; 8 when the launch would otherwise leave most SMs empty (batch-1 latency:
+// 2 clouds x 1024 centres are only 64 warps of 32 centres).  Lanes >= CPW own no centre; rows are packed the same way.
+template <int CIN, int H1, int H2, int H3, int CPW>
 __global__ void __launch_bounds__(SA_WARPS * 32)
 sa_mlp_kernel(const __grid_constant__ SaParams a) {
     static_assert(H3 == 32, "lane <-> channel reduction assumes 32 output channels");
     __shared__ float s_tile[SA_WARPS][32][33];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int b = blockIdx.y;
-    const int c0 = (blockIdx.x * SA_WARPS + warp) * 32;
+    const int c0 = (blockIdx.x * SA_WARPS + warp) * CPW;
     if (c0 >= a.M) return;
     const int c = c0 + lane;
-    const bool has_c = c < a.M;
+    const bool has_c = lane < CPW && c < a.M;
     const float *ctr = a.new_xyz + ((size_t)b * a.M + (has_c ? c : c0)) * 3;
     const float ccx = __ldg(ctr), ccy = __ldg(ctr + 1), ccz = __ldg(ctr + 2);
     const float *xb = a.x + (size_t)b * a.N * CIN;
@@ -154,9 +156,17 @@ int sa_mlp_launch(const SaArgs &s, int B, int cin, const int *h, cudaStream_t st
         p.idx[i] = s.idx[i]; p.cnt[i] = s.cnt[i]; p.ns[i] = s.ns[i];
         for (int e = 0; e < SA_WMAX; ++e) p.w[i][e] = (i < s.nscales && e < wsz) ? s.w_host[i][e] : 0.f;
     }
-    dim3 grid(div_up(s.M, SA_WARPS * 32), B);
-    if (cin == 4) sa_mlp_kernel<4, 16, 16, 32><<<grid, SA_WARPS * 32, 0, st>>>(p);
-    else sa_mlp_kernel<3, 16, 16, 32><<<grid, SA_WARPS * 32, 0, st>>>(p);
+    // few centres in the whole launch (small batches): 8 centres per warp spread them over 4x as many warps
+    const bool small = (long long)B * s.M < 148LL * SA_WARPS * 32;
+    if (small) {
+        dim3 grid(div_up(s.M, SA_WARPS * 8), B);
+        if (cin == 4) sa_mlp_kernel<4, 16, 16, 32, 8><<<grid, SA_WARPS * 32, 0, st>>>(p);
+        else sa_mlp_kernel<3, 16, 16, 32, 8><<<grid, SA_WARPS * 32, 0, st>>>(p);
+    } else {
+        dim3 grid(div_up(s.M, SA_WARPS * 32), B);
+        if (cin == 4) sa_mlp_kernel<4, 16, 16, 32, 32><<<grid, SA_WARPS * 32, 0, st>>>(p);
+        else sa_mlp_kernel<3, 16, 16, 32, 32><<<grid, SA_WARPS * 32, 0, st>>>(p);
+    }
     DCLR_LAUNCH_CHECK("sa_mlp_kernel");
     return DCLR_OK;
 }
