@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument('--no-latency', action='store_true', help='skip the batch-1 latency loop (ncu launch lists)')
     ap.add_argument('--no-raw-scans', action='store_true', help='skip the raw-scan front-end arm (e2e_raw_scans)')
     ap.add_argument('--raw-points', type=int, default=120000, help='mean points of a raw scan (KITTI HDL-64: ~120 k)')
-    ap.add_argument('--cpu-pairs', type=int, default=8, help='pairs of the bounded CPU sample')
+    ap.add_argument('--cpu-pairs', type=int, default=40, help='pairs of the bounded CPU sample')
     return ap.parse_args()
 
 

@@ -24,6 +24,10 @@ def install_as_deepclr() -> None:
                           ('deepclr.config', 'deepclr_b200.config'),
                           ('deepclr.data', 'deepclr_b200.data'),
                           ('deepclr.data.labels', 'deepclr_b200.data.labels'),
+                          ('deepclr.data.datasets', 'deepclr_b200.data.datasets'),
+                          ('deepclr.data.datasets.kitti', 'deepclr_b200.data.datasets.kitti'),
+                          ('deepclr.evaluation', 'deepclr_b200.evaluation'),
+                          ('deepclr.evaluation.data', 'deepclr_b200.evaluation.data'),
                           ('deepclr.utils', 'deepclr_b200.utils'),
                           ('deepclr.models', 'deepclr_b200.models'),
                           ('deepclr.models.deepclr', 'deepclr_b200.models.deepclr'),

@@ -133,3 +133,17 @@ def test_result_files_equal_the_reference_writer(tmp_path):
     r1, r2 = Sequence.read(str(tmp_path / 'b.txt')), ref.Sequence.read(str(tmp_path / 'a.txt'))
     for a, b in zip(r1.ground_truth.poses, r2.ground_truth.poses):
         np.testing.assert_allclose(a, b, atol=1e-12)
+
+
+def test_reference_import_names_resolve():
+    """`deepclr_b200.install_as_deepclr()` makes the reference's import lines for these modules work unchanged
+    (scripts/inference.py, scripts/evaluation.py)."""
+    import subprocess
+    code = ("import deepclr_b200; deepclr_b200.install_as_deepclr();"
+            "from deepclr.evaluation.data import Sequence, Motion;"
+            "from deepclr.data.datasets.kitti import KittiOdometryVelodyneData, KittiOdometryVelodyneSequenceData, cam2velo, velo2cam;"
+            "from deepclr.data.labels import LabelType;"
+            "from deepclr.models import ModelInferenceHelper, build_model, load_trained_model;"
+            "from deepclr.config import load_model_config")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call([sys.executable, '-c', code], cwd=root)
