@@ -325,6 +325,22 @@ def run_native(args, rank, world, local_rank):
             b.synchronize()
             lat.append(a.elapsed_time(b))
     lat.sort()
+    # the same single-pair forward replayed from a CUDA graph (deepclr_b200.models.GraphedForward): one launch per call
+    lat_graph = []
+    if not args.no_latency:
+        from deepclr_b200.models import GraphedForward
+        gf = GraphedForward(model, one[0])
+        for i in range(10):
+            gf(one[i % ROTATE])
+        for i in range(50):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            gf(one[i % ROTATE])
+            b.record()
+            b.synchronize()
+            lat_graph.append(a.elapsed_time(b))
+        lat_graph.sort()
+        del gf
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -377,7 +393,9 @@ def run_native(args, rank, world, local_rank):
                        'l2': f'{ROTATE} distinct resident input batches cycled + >126 MB of per-step workspace traffic'},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof,
             'stage_ms': per_call, 'roofline_stages': roof_stages,
-            'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat)},
+            'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat),
+                           'p50_graph_ms': lat_graph[len(lat_graph) // 2] if lat_graph else None,
+                           'p90_graph_ms': lat_graph[int(len(lat_graph) * 0.9)] if lat_graph else None},
             'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
     if e2e_raw is not None:
         line['e2e_raw_scans'] = e2e_raw

@@ -145,3 +145,37 @@ class RawScanPipeline(HostPipeline):
         x = dev_ops.subsample_clouds(rc, self.n_points, seed=self.seed + self._batch_no)
         self._batch_no += 1
         return self.model(x)[0]
+
+
+class GraphedForward:
+    """The whole fused forward of ONE input shape captured in a CUDA graph: `y = GraphedForward(model, x_example)(x)`.
+    For the latency case (one pair per call, `scripts/inference.py:104`): the ~11 kernels of a forward, the fork / join
+    of the ball-query grid build and the output allocation become one graph launch, so the CPU-side launch cost and
+    the gaps between small kernels disappear.  `x` is copied into the graph's static input buffer (device -> device, or
+    host -> device when it is a pinned CPU tensor); the returned poses are a static buffer that the next call overwrites
+    (clone to keep)."""
+
+    def __init__(self, model, example: torch.Tensor, warmup: int = 3):
+        dev = next(model.parameters()).device
+        if dev.type != 'cuda':
+            raise RuntimeError('GraphedForward needs the model on a CUDA device: there is no CPU path')
+        self.model = model
+        self.static_x = torch.empty(tuple(example.shape), dtype=torch.float32, device=dev)
+        self.static_x.copy_(example)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):      # sizes the native workspace, creates the side stream: no cudaMalloc later
+                model(self.static_x)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.static_y = model(self.static_x)[0]
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if tuple(x.shape) != tuple(self.static_x.shape):
+            raise ValueError(f'graph captured for {tuple(self.static_x.shape)}, got {tuple(x.shape)}')
+        self.static_x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.static_y
