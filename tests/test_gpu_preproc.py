@@ -214,3 +214,41 @@ def test_filter_random_ragged_batches(dev_ops):
             want = preproc.filter_cloud(c, nth, start, rmin, rmax, out_dim)
             assert counts[b] == want.shape[0], (trial, b)
             assert np.array_equal(_rows(out, b), want, equal_nan=True), (trial, b)
+
+
+def test_kernels_write_only_what_they_own():
+    """Own bounds check (compute-sanitizer is not available on the pool): outputs pre-filled with a sentinel; the
+    filter may touch only the first counts[b] rows of every cloud's slot, the subsample only its [B, N, C] block; guard
+    rows behind both stay intact."""
+    from deepclr_b200 import _lib
+    rng = np.random.Generator(np.random.PCG64(77))
+    S = -12345.0
+    for C, out_dim in ((4, 4), (5, 3)):
+        sizes = [5000, 0, 2048, 1, 4097, 333, 2049]
+        clouds = [rng.uniform(-60, 60, (n, C)).astype(np.float32) for n in sizes]
+        off_h = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+        total, guard = int(off_h[-1]), 4096
+        pts = torch.from_numpy(np.concatenate(clouds)).to(DEV)
+        off = torch.from_numpy(off_h).to(DEV)
+        out = torch.full((total + guard, out_dim), S, device=DEV)
+        cnt = torch.full((len(sizes) + 8,), -7, dtype=torch.int32, device=DEV)
+        _lib.check(_lib.lib().dclr_filter_clouds(_lib.ptr(pts), _lib.ptr(off), len(sizes), max(sizes), C, out_dim, 3, 1,
+                                                 2.0, 50.0, _lib.ptr(out), _lib.ptr(cnt), _lib.stream_ptr()), 'filter')
+        o, c = out.cpu().numpy(), cnt.cpu().numpy()
+        assert (c[len(sizes):] == -7).all() and (o[total:] == S).all()
+        for b, cl in enumerate(clouds):
+            want = preproc.filter_cloud(cl, 3, 1, 2.0, 50.0, out_dim)
+            assert c[b] == want.shape[0]
+            assert np.array_equal(o[off_h[b]:off_h[b] + c[b]], want)
+            assert (o[off_h[b] + c[b]:off_h[b + 1]] == S).all(), (C, b)
+        n_out = 300
+        x = torch.full((len(sizes) * n_out + guard, out_dim), S, device=DEV)
+        perm = torch.full((len(sizes) * n_out + guard,), -9, dtype=torch.int32, device=DEV)
+        _lib.check(_lib.lib().dclr_subsample_clouds(_lib.ptr(out), _lib.ptr(off), _lib.ptr(cnt), len(sizes), out_dim,
+                                                    out_dim, n_out, 5, 1, _lib.ptr(x), _lib.ptr(perm), None,
+                                                    _lib.stream_ptr()), 'subsample')
+        assert (x[len(sizes) * n_out:] == S).all() and (perm[len(sizes) * n_out:] == -9).all()
+        assert not (x[:len(sizes) * n_out] == S).any()
+        p = perm[:len(sizes) * n_out].view(len(sizes), n_out).cpu().numpy()
+        for b in range(len(sizes)):
+            assert p[b].max() < max(int(c[b]), 1) and p[b].min() >= (-1 if c[b] == 0 else 0)
