@@ -14,104 +14,108 @@ from typing import List
 import numpy as np
 
 
-def _vec_to_mat(v: np.ndarray) -> np.ndarray:
-    m = np.eye(4)
-    m[:3, :4] = np.asarray(v, dtype=np.float64).reshape(3, 4)
-    return m
+def _vec_to_mat(v) -> np.ndarray:
+    """12 row-major numbers -> homogeneous 4x4."""
+    return np.vstack([np.asarray(v, dtype=np.float64).reshape(3, 4), [0.0, 0.0, 0.0, 1.0]])
 
 
-def _mat_to_vec(m: np.ndarray) -> np.ndarray:
+def _mat_to_vec(m) -> np.ndarray:
     return np.asarray(m)[:3, :4].reshape(12)
 
 
+def _load_rows(filename: str) -> np.ndarray:
+    return np.loadtxt(filename, ndmin=2)
+
+
 class Motion:
+    """`transforms[i]` moves frame i to frame i+1, `poses[i]` is the accumulated pose of frame i (poses[0] = identity when
+    fed with transforms), `distances[i]` the path length travelled up to frame i."""
+
     def __init__(self) -> None:
         self.transforms: List[np.ndarray] = []
         self.poses: List[np.ndarray] = []
         self.distances: List[float] = []
 
-    def _step(self, transform: np.ndarray) -> None:
-        self.transforms.append(transform)
-        self.distances.append(self.distances[-1] + float(np.linalg.norm(transform[:3, 3])))
+    def _advance(self, step: np.ndarray, pose: np.ndarray) -> None:
+        travelled = self.distances[-1] + float(np.linalg.norm(step[:3, 3]))
+        self.transforms += [step]
+        self.poses += [pose]
+        self.distances += [travelled]
 
     def add_transform(self, m: np.ndarray) -> None:
         """Relative motion of the next frame; the first call also creates the identity start pose."""
         if not self.poses:
-            self.poses.append(np.eye(4))
-            self.distances.append(0)
-        self.poses.append(self.poses[-1] @ m)
-        self._step(m)
+            self.poses, self.distances = [np.eye(4)], [0]
+        self._advance(m, self.poses[-1] @ m)
 
     def add_pose(self, m: np.ndarray) -> None:
         """Absolute pose of the next frame; from the second one on the transform to the previous pose is derived."""
-        self.poses.append(m)
-        if len(self.poses) == 1:
-            self.distances.append(0)
+        if self.poses:
+            self._advance(np.linalg.inv(self.poses[-1]) @ m, m)
         else:
-            self._step(np.linalg.inv(self.poses[-2]) @ m)
+            self.poses, self.distances = [m], [0]
 
     def get_path(self) -> np.ndarray:
-        return np.array([p[:3, 3] for p in self.poses])
+        return np.stack([p[:3, 3] for p in self.poses]) if self.poses else np.zeros((0, 3))
 
     def get_frame_by_distance(self, first_frame: int, distance: float) -> int:
         """First frame that lies more than `distance` of travelled path behind `first_frame`, -1 if none."""
-        limit = self.distances[first_frame] + distance
-        for i in range(first_frame, len(self.distances)):
-            if self.distances[i] > limit:
-                return i
-        return -1
+        d = np.asarray(self.distances[first_frame:], dtype=np.float64)
+        hits = np.nonzero(d > self.distances[first_frame] + distance)[0]
+        return int(first_frame + hits[0]) if hits.size else -1
 
     @classmethod
     def read(cls, filename: str, has_poses: bool) -> Motion:
         """As the reference (data.py:63-72): `has_poses=True` treats the rows as relative transforms."""
-        motion = cls()
-        for row in np.loadtxt(filename, ndmin=2):
-            (motion.add_transform if has_poses else motion.add_pose)(_vec_to_mat(row[:12]))
-        return motion
+        out = cls()
+        feed = out.add_transform if has_poses else out.add_pose
+        for row in _load_rows(filename):
+            feed(_vec_to_mat(row[:12]))
+        return out
 
     def write(self, filename: str, use_poses: bool) -> None:
         np.savetxt(filename, np.array([_mat_to_vec(m) for m in (self.poses if use_poses else self.transforms)]))
 
 
 class Sequence:
+    """Predicted and ground-truth motion of one run with the frame stamps and inference times."""
+
     def __init__(self) -> None:
-        self.prediction = Motion()
-        self.ground_truth = Motion()
+        self.prediction, self.ground_truth = Motion(), Motion()
         self.stamps: list = []
         self.times: list = []
 
+    def _push(self, how: str, stamp: float, pred: np.ndarray, gt: np.ndarray, time: float) -> None:
+        self.stamps += [stamp]
+        self.times += [time]
+        getattr(self.prediction, how)(pred)
+        getattr(self.ground_truth, how)(gt)
+
     def add_transforms(self, stamp: float, pred: np.ndarray, gt: np.ndarray, time: float = 0) -> None:
-        self.stamps.append(stamp)
-        self.times.append(time)
-        self.prediction.add_transform(pred)
-        self.ground_truth.add_transform(gt)
+        self._push('add_transform', stamp, pred, gt, time)
 
     def add_poses(self, stamp: float, pred: np.ndarray, gt: np.ndarray, time: float = 0) -> None:
-        self.stamps.append(stamp)
-        self.times.append(time)
-        self.prediction.add_pose(pred)
-        self.ground_truth.add_pose(gt)
+        self._push('add_pose', stamp, pred, gt, time)
 
     @classmethod
     def read(cls, filename: str) -> Sequence:
-        seq = cls()
-        for row in np.loadtxt(filename, ndmin=2):
-            seq.add_transforms(row[0], _vec_to_mat(row[1:13]), _vec_to_mat(row[13:25]), row[25])
-        return seq
+        out = cls()
+        for row in _load_rows(filename):
+            out.add_transforms(row[0], _vec_to_mat(row[1:13]), _vec_to_mat(row[13:25]), row[25])
+        return out
 
     @classmethod
     def read_separate(cls, filename_pred: str, filename_gt: str, has_poses: bool) -> Sequence:
-        seq = cls()
-        seq.prediction = Motion.read(filename_pred, has_poses)
-        seq.ground_truth = Motion.read(filename_gt, has_poses)
-        n = len(seq.prediction.transforms)
-        if len(seq.ground_truth.transforms) != n:
+        out = cls()
+        out.prediction, out.ground_truth = Motion.read(filename_pred, has_poses), Motion.read(filename_gt, has_poses)
+        n = len(out.prediction.transforms)
+        if n != len(out.ground_truth.transforms):
             raise RuntimeError("Sizes of prediction and ground truth files do not match.")
-        seq.stamps = np.arange(n).tolist()
-        seq.times = np.zeros(n).tolist()
-        return seq
+        out.stamps, out.times = list(range(n)), [0.0] * n
+        return out
 
     def write(self, filename: str) -> None:
-        rows = [np.concatenate(([s], _mat_to_vec(p), _mat_to_vec(g), [t])) for s, p, g, t in
-                zip(self.stamps, self.prediction.transforms, self.ground_truth.transforms, self.times)]
-        np.savetxt(filename, np.array(rows))
+        # one row per TRANSFORM: fed with poses there is one transform less than stamps, the surplus stamp is dropped
+        rows = zip(self.stamps, self.prediction.transforms, self.ground_truth.transforms, self.times)
+        table = [np.concatenate(([s], _mat_to_vec(p), _mat_to_vec(g), [t])) for s, p, g, t in rows]
+        np.savetxt(filename, np.array(table))
