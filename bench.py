@@ -113,7 +113,27 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.rows, self._halt = index, [], threading.Event()
 
+    def _run_nvml(self):
+        """NVML in-process (nvidia_ml_py): ~0.1 ms per sample, so even a 25 ms timed region gets tens of samples."""
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        bits = [0x8, 0x40, 0x20, 0x4]       # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
+        while not self._halt.is_set():
+            r = get_reasons(h)
+            self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx),
+                              str(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)] +
+                             ['Active' if r & b else 'Not Active' for b in bits])
+            self._halt.wait(0.001)
+
     def run(self):
+        try:
+            self._run_nvml()
+            return
+        except Exception:
+            pass
         while not self._halt.is_set():
             try:
                 o = subprocess.run(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
