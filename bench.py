@@ -112,29 +112,59 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self._halt = index, [], threading.Event()
+        # NVML is initialised HERE, before the timed region starts (nvmlInit alone can take longer than the region);
+        # the thread then only polls: ~0.1 ms per sample
+        self._nv = self._h = None
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            self._h = nv.nvmlDeviceGetHandleByIndex(index)
+            self._max = nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM)
+            self._reasons = (getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None)
+                             or nv.nvmlDeviceGetCurrentClocksThrottleReasons)
+            self._nv = nv
+            self._sample_nvml()
+            self.rows.clear()                        # that one only proved the calls work
+        except Exception as e:
+            self._nv = None
+            print(f'[bench] NVML unavailable ({type(e).__name__}: {e}); clocks come from nvidia-smi', file=sys.stderr)
+
+    def _sample_nvml(self):
+        nv, h = self._nv, self._h
+        r = self._reasons(h)
+        bits = [0x8, 0x40, 0x20, 0x4]       # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
+        self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(self._max),
+                          str(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)] +
+                         ['Active' if r & b else 'Not Active' for b in bits])
 
     def _run_nvml(self):
-        """NVML in-process (nvidia_ml_py): ~0.1 ms per sample, so even a 25 ms timed region gets tens of samples."""
-        import pynvml as nv
-        nv.nvmlInit()
-        h = nv.nvmlDeviceGetHandleByIndex(self.index)
-        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-        get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
-        bits = [0x8, 0x40, 0x20, 0x4]       # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
         while not self._halt.is_set():
-            r = get_reasons(h)
-            self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx),
-                              str(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)] +
-                             ['Active' if r & b else 'Not Active' for b in bits])
+            self._sample_nvml()
             self._halt.wait(0.001)
 
     def run(self):
         try:
-            self._run_nvml()
-            return
-        except Exception:
-            pass
+            if self._nv is not None:
+                self._run_nvml()
+                return
+        except Exception as e:                      # reported, then the nvidia-smi route takes over
+            print(f'[bench] NVML clock sampling failed ({type(e).__name__}: {e}); falling back to nvidia-smi',
+                  file=sys.stderr, flush=True)
         while not self._halt.is_set():
+            try:
+                o = subprocess.run(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                    '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                f = [v.strip() for v in o.strip().split(',')]
+                if len(f) >= 7:
+                    self.rows.append(f)
+            except Exception as e:
+                print(f'[bench] nvidia-smi clock sample failed ({type(e).__name__}: {e})', file=sys.stderr, flush=True)
+            self._halt.wait(0.1)
+
+    def finish(self):
+        self._halt.set()
+        self.join(6)
+        if not self.rows:                            # region shorter than one nvidia-smi call: one sample right after it
             try:
                 o = subprocess.run(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
                                     '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
@@ -143,11 +173,6 @@ class ClockSampler(threading.Thread):
                     self.rows.append(f)
             except Exception:
                 pass
-            self._halt.wait(0.1)
-
-    def finish(self):
-        self._halt.set()
-        self.join(6)
         if not self.rows:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
         sm = sorted(float(r[0]) for r in self.rows)
