@@ -205,8 +205,9 @@ def run_reference(args, rank, world):
     needs /root/reference and third-party wheels that do not exist on the GPU box).  Rank 0 only."""
     if rank != 0:
         return
-    per_step = max(1, args.cpu_pairs // 4)
+    per_step = max(1, args.cpu_pairs // 10)
     import torch
+    torch.set_num_threads(os.cpu_count() or 1)     # torchrun exports OMP_NUM_THREADS=1 per rank; this arm owns the host
     from oracle import model_oracle, ops
     model, cfg = build_model_and_cfg(args.kind)
     sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
@@ -444,7 +445,7 @@ def run_native(args, rank, world, local_rank):
             'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
     if e2e_raw is not None:
         line['e2e_raw_scans'] = e2e_raw
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:      # reported at N=1 only (rank 0 owns the host cores there)
         v, cores, dt = cpu_oracle_pairs_per_s(args.kind, args.points, args.cpu_pairs)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
                                 'sample': f'{args.cpu_pairs} batch-1 forwards of {N}-point pairs ({dt:.1f} s)'}
@@ -469,6 +470,10 @@ def claim_stdout():
 def main():
     args = parse_args()
     claim_stdout()
+    if args.impl == 'reference':
+        # rank 0 alone works in this arm and may use every host core: undo torchrun's OMP_NUM_THREADS=1 before libgomp
+        # (torch, the C oracle) is loaded
+        os.environ['OMP_NUM_THREADS'] = str(os.cpu_count() or 1)
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local_rank = int(os.environ.get('LOCAL_RANK', 0))
