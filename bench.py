@@ -291,7 +291,8 @@ def run_native(args, rank, world, local_rank):
     # pinned host memory and reads its poses back to the host inside the timed region; the copy of step i+1 is issued on
     # a copy stream while step i computes (double-buffered device inputs), the host collects the poses of step i-1.
     from deepclr_b200.models import HostPipeline
-    pipe = HostPipeline(model, depth=2)
+    use_graph = os.environ.get('DCLR_GRAPH', '1') == '1'
+    pipe = HostPipeline(model, depth=2, use_cuda_graph=use_graph)
     pipe.run_all(host[i % ROTATE] for i in range(max(3, args.warmup // 2)))
     pipe.h2d_bytes = pipe.d2h_bytes = 0
     e2e_out = []
@@ -312,7 +313,7 @@ def run_native(args, rank, world, local_rank):
     assert len(e2e_out[0]) == args.steps and all(torch.isfinite(o).all() for o in e2e_out[0])
     e2e = {'value': world * B * args.steps / (ms_e2e * 1e-3), 'unit': 'pairs/s',
            'h2d_bytes_per_step': pipe.h2d_bytes // args.steps, 'd2h_bytes_per_step': pipe.d2h_bytes // args.steps,
-           'ms_per_step': ms_e2e / args.steps, 'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches)'}
+           'ms_per_step': ms_e2e / args.steps, 'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches%s)' % (', forward replayed from CUDA graphs' if use_graph else '')}
 
     # ---- raw-scan arm: what the reference's inference loop does before its batch copy -- every
     # 2nd point, range filter, random subsample to N points, per scan in numpy on the host (transforms/build.py:37-39)

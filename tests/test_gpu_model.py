@@ -202,3 +202,16 @@ def test_inference_helper_with_cuda_graph():
         x = torch.from_numpy(synth.batch('kitti', 1, 400 + i, n=int(g['n']))).to(DEV)
         assert torch.equal(plain.predict(x[1], x[0]), graphed.predict(x[1], x[0]))
     assert len(graphed._graphs) == 1
+
+
+def test_host_pipeline_with_cuda_graph_equals_plain():
+    from deepclr_b200 import synth
+    from deepclr_b200.models import HostPipeline
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    batches = [torch.from_numpy(synth.batch('kitti', 2, 500 + i, n=int(g['n']))).pin_memory() for i in range(7)]
+    plain = HostPipeline(model).run_all(batches)
+    graphed = HostPipeline(model, use_cuda_graph=True).run_all(batches)
+    assert len(plain) == len(graphed) == 7
+    for a, b in zip(plain, graphed):
+        assert torch.equal(a, b)
