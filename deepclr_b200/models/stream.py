@@ -62,7 +62,7 @@ class HostPipeline:
             y = self.model(x)[0]
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, capture_error_mode='thread_local'):   # other threads (NCCL watchdog) may call CUDA
                 y_static = self.model(x)[0]
             self._graphs[slot] = (key, g, y_static)
             return y
@@ -197,7 +197,7 @@ class GraphedForward:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph), torch.no_grad():
+        with torch.cuda.graph(self.graph, capture_error_mode='thread_local'), torch.no_grad():
             self.static_y = model(self.static_x)[0]
 
     def replay(self) -> torch.Tensor:
