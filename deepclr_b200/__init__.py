@@ -37,18 +37,20 @@ def install_as_deepclr() -> None:
 
 
 FPS_TIE_RULES = {'lowest_index': 0, 'reference': 1}
+_fps_tie_rule = 'reference'
 
 
 def set_fps_tie_rule(rule: str) -> None:
-    """How farthest point sampling resolves bit-equal maxima (include/deepclr_b200.h: dclr_set_fps_tie_rule).
-    'lowest_index' (default, BASELINE.json's stated rule) or 'reference' (the order of the reference's
-    furthest_point_sampling_kernel, sampling_gpu.cu:113-203 -- indices then match that kernel on every input)."""
-    from . import _lib
+    """Host-side default of how farthest point sampling orders bit-equal maxima: what `furthest_point_sample` and
+    models without an own `fps_tie_rule` pass down (the C ABI itself holds no global: the rule is an argument of
+    dclr_fps and a property of a model handle, include/deepclr_b200.h).
+    'reference' (default): the order of the reference's furthest_point_sampling_kernel (sampling_gpu.cu:113-203) --
+    indices equal that kernel's on every input.  'lowest_index': the rule BASELINE.json states."""
+    global _fps_tie_rule
     if rule not in FPS_TIE_RULES:
         raise ValueError(f'rule must be one of {sorted(FPS_TIE_RULES)}')
-    _lib.check(_lib.lib().dclr_set_fps_tie_rule(FPS_TIE_RULES[rule]), 'dclr_set_fps_tie_rule')
+    _fps_tie_rule = rule
 
 
 def get_fps_tie_rule() -> str:
-    from . import _lib
-    return {v: k for k, v in FPS_TIE_RULES.items()}[_lib.lib().dclr_get_fps_tie_rule()]
+    return _fps_tie_rule

@@ -26,9 +26,7 @@ class DclrArch(ctypes.Structure):
 _SIGNATURES = {
     'dclr_version': (ctypes.c_char_p, []),
     'dclr_last_error': (ctypes.c_char_p, []),
-    'dclr_set_fps_tie_rule': (ctypes.c_int, [ctypes.c_int]),
-    'dclr_get_fps_tie_rule': (ctypes.c_int, []),
-    'dclr_fps': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    'dclr_fps': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_gather': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_pose_to_matrix': (c_int, [c_void_p, c_int, c_int, ctypes.c_float, c_void_p, c_void_p]),
     'dclr_pose_errors': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
@@ -45,6 +43,8 @@ _SIGNATURES = {
     'dclr_model_create': (c_int, [ctypes.POINTER(DclrArch), c_void_p, c_size_t, ctypes.POINTER(c_void_p)]),
     'dclr_model_destroy': (None, [c_void_p]),
     'dclr_model_set_numerics': (c_int, [c_void_p, c_int]),
+    'dclr_model_set_fps_tie_rule': (c_int, [c_void_p, c_int]),
+    'dclr_model_get_fps_tie_rule': (c_int, [c_void_p]),
     'dclr_cloud_features': (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     'dclr_forward_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_forward_pairs': (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -230,10 +230,10 @@ static int launch_resident(const float *pts, int stride, int B, int N, int npoin
     return DCLR_OK;
 }
 
-int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *nx, float *temp_big,
-               cudaStream_t st) {
+int fps_launch(const float *pts, int stride, int B, int N, int npoint, int tie_rule, int32_t *idx, float *nx,
+               float *temp_big, cudaStream_t st) {
     int tieL = -1;
-    if (fps_tie_rule() == 1)
+    if (tie_rule == DCLR_TIE_REFERENCE)
         for (tieL = 0; (2 << tieL) <= N && tieL < 10; ++tieL) {}          // log2(opt_n_threads(N)), cuda_utils.h:10-14
     // T threads x PP pairs x 2 points >= N
     if (N <= 256) return launch_resident<128, 1, false>(pts, stride, B, N, npoint, tieL, idx, nx, st);
@@ -251,10 +251,12 @@ int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *
 
 }  // namespace dclr
 
-extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int32_t *idx_out,
+extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int tie_rule, int32_t *idx_out,
                         float *new_xyz_out, void *stream) {
     using namespace dclr;
     DCLR_CHECK_ARG(pts && idx_out, "dclr_fps: null pointer");
+    DCLR_CHECK_ARG(tie_rule == DCLR_TIE_LOWEST_INDEX || tie_rule == DCLR_TIE_REFERENCE,
+                   "dclr_fps: tie_rule must be 0 (lowest index) or 1 (reference kernel order), got %d", tie_rule);
     DCLR_CHECK_ARG(pt_stride >= 3 && B >= 0 && N >= 1 && npoint >= 0, "dclr_fps: bad shape B=%d N=%d npoint=%d stride=%d",
                    B, N, npoint, pt_stride);
     if (B == 0 || npoint == 0) return DCLR_OK;
@@ -263,13 +265,13 @@ extern "C" int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoin
         void *ws = nullptr;
         { int rc_ = scratch_alloc(&ws, fps_bucket_workspace_bytes(B, N), st); if (rc_ != DCLR_OK) return rc_; }
         int used = 0;
-        int rc = fps_bucket_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, ws, st, &used);
+        int rc = fps_bucket_launch(pts, pt_stride, B, N, npoint, tie_rule, idx_out, new_xyz_out, ws, st, &used);
         scratch_free(ws, st);
         if (rc != DCLR_OK || used) return rc;
     }
     float *temp = nullptr;
     if (N > FPS_MAX_RESIDENT_N) { int rc_ = scratch_alloc((void **)&temp, (size_t)B * N * sizeof(float), st); if (rc_ != DCLR_OK) return rc_; }
-    int rc = fps_launch(pts, pt_stride, B, N, npoint, idx_out, new_xyz_out, temp, st);
+    int rc = fps_launch(pts, pt_stride, B, N, npoint, tie_rule, idx_out, new_xyz_out, temp, st);
     scratch_free(temp, st);
     return rc;
 }

@@ -7,9 +7,9 @@
 namespace dclr {
 
 // fps.cu
-int fps_tie_rule();        // 0 = lowest index, 1 = the reference kernel's tree order (core.cu)
-int fps_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, float *temp_big,
-               cudaStream_t st);
+// tie_rule: DCLR_TIE_LOWEST_INDEX / DCLR_TIE_REFERENCE (include/deepclr_b200.h); an argument of every launch, no global state
+int fps_launch(const float *pts, int stride, int B, int N, int npoint, int tie_rule, int32_t *idx, float *new_xyz,
+               float *temp_big, cudaStream_t st);
 
 // fps_bucket.cu: exact pruned FPS for 8192 < N <= 131072 (smaller clouds: the resident kernel is faster); *used = 0
 // when the shape is not handled
@@ -17,8 +17,8 @@ size_t fps_bucket_workspace_bytes(int B, int N);
 int fps_bucket_l2_launch(const float4 *sorted, float *tmin, int B, int N, int npoint, int tieL, int32_t *idx, float *nx,
                          cudaStream_t st);
 // after_sort (optional) is recorded on st between the sort and the sampling kernel
-int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int32_t *idx, float *new_xyz, void *ws,
-                      cudaStream_t st, int *used, cudaEvent_t after_sort = nullptr);
+int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int tie_rule, int32_t *idx, float *new_xyz,
+                      void *ws, cudaStream_t st, int *used, cudaEvent_t after_sort = nullptr);
 
 // pointops.cu
 int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B, int N, int M, int nr,

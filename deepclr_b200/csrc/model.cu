@@ -15,6 +15,7 @@ struct dclr_model {
     struct Lin { const float *W, *b; int out, in; };
     Lin merge[3], outc[5], lin[2], fin;
     int numerics = 0;
+    int tie_rule = DCLR_TIE_REFERENCE;   // FPS tie order (dclr_model_set_fps_tie_rule)
     // workspace
     void *ws = nullptr;
     size_t ws_bytes = 0;
@@ -152,11 +153,12 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     {
         StageScope sc(m, ST_FPS, st);
         int used = 0;
-        DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_ws, st, &used, m->ev_fork));
+        DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->tie_rule, m->fps_idx, m->new_xyz, m->fps_ws, st, &used,
+                                   m->ev_fork));
         if (used) ++m->last_launches;                      // sort + sample
         else {
             DCLR_CUDA(cudaEventRecord(m->ev_fork, st));
-            DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->fps_idx, m->new_xyz, m->fps_temp, st));
+            DCLR_TRY(fps_launch(x, a.input_dim, G, N, a.npoint, m->tie_rule, m->fps_idx, m->new_xyz, m->fps_temp, st));
         }
     }
     {
@@ -367,6 +369,15 @@ extern "C" int dclr_model_set_numerics(dclr_model *m, int mode) {
     m->numerics = mode;
     return DCLR_OK;
 }
+
+extern "C" int dclr_model_set_fps_tie_rule(dclr_model *m, int rule) {
+    DCLR_CHECK_ARG(m, "null model");
+    DCLR_CHECK_ARG(rule == DCLR_TIE_LOWEST_INDEX || rule == DCLR_TIE_REFERENCE,
+                   "dclr_model_set_fps_tie_rule: rule must be 0 (lowest index) or 1 (reference kernel order), got %d", rule);
+    m->tie_rule = rule;
+    return DCLR_OK;
+}
+extern "C" int dclr_model_get_fps_tie_rule(const dclr_model *m) { return m ? m->tie_rule : -1; }
 
 extern "C" int dclr_cloud_features(dclr_model *m, const float *x, int num_clouds, int N, float *feat_out,
                                    void *stream) {

@@ -331,6 +331,7 @@ class DeepCLR(BaseModel):
             self._loss_layer = init_loss_module(_as_cfg(loss), label_type, **kwargs)
         # fused route state
         self.numerics = os.environ.get('DCLR_NUMERICS', 'fp32')   # 'fp32' | 'fp16' | 'bf16' (include/deepclr_b200.h)
+        self.fps_tie_rule: Optional[str] = None    # None = deepclr_b200.get_fps_tie_rule() at call time ('reference')
         self._native: Optional[NativeModel] = None
         self._native_key = None
 
@@ -414,7 +415,9 @@ class DeepCLR(BaseModel):
 
     def _get_native(self, device: torch.device) -> NativeModel:
         pairs = self._dense_layers()
-        key = (str(device), self.numerics) + tuple((p.data_ptr(), p._version) for layer, _ in pairs
+        import deepclr_b200
+        tie_rule = self.fps_tie_rule or deepclr_b200.get_fps_tie_rule()
+        key = (str(device), self.numerics, tie_rule) + tuple((p.data_ptr(), p._version) for layer, _ in pairs
                                                    for p in layer.parameters())
         if self._native is None or key != self._native_key:
             sa, me, out = self._cloud_layers[-1], self._merge_layers[0], self._merge_layers[1]
@@ -438,6 +441,6 @@ class DeepCLR(BaseModel):
             for l, block in enumerate(out.linear._sequential):
                 arch.out_linear[l + 1] = block.output_dim()
             arch.label_type = self._label_type.native_id
-            self._native = NativeModel(arch, pairs, device, self.numerics)
+            self._native = NativeModel(arch, pairs, device, self.numerics, tie_rule)
             self._native_key = key
         return self._native

@@ -31,7 +31,7 @@ class NativeModel:
     """Owns one `dclr_model*` on one device."""
 
     def __init__(self, arch: _lib.DclrArch, layers: List[Tuple[nn.Module, Optional[nn.Module]]], device: torch.device,
-                 numerics: str):
+                 numerics: str, fps_tie_rule: str = 'reference'):
         blobs = []
         for layer, norm in layers:
             w, b = _fold(layer, norm)
@@ -44,7 +44,11 @@ class NativeModel:
                                                     flat.numel(), ctypes.byref(self._handle)), 'dclr_model_create')
             _lib.check(_lib.lib().dclr_model_set_numerics(self._handle, {'fp32': 0, 'bf16': 1, 'fp16': 2}[numerics]),
                        'dclr_model_set_numerics')
+            from .. import FPS_TIE_RULES
+            _lib.check(_lib.lib().dclr_model_set_fps_tie_rule(self._handle, FPS_TIE_RULES[fps_tie_rule]),
+                       'dclr_model_set_fps_tie_rule')
         self.numerics = numerics
+        self.fps_tie_rule = fps_tie_rule
         self.label_dim = {0: 6, 1: 7, 2: 8}[arch.label_type]
         self.npoint = arch.npoint
         self.feat_dim = 3 + sum(arch.sa_mlp[s][2] for s in range(arch.num_scales))

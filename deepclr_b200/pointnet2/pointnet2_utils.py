@@ -11,6 +11,11 @@ from torch.autograd import Function
 from .. import _lib
 
 
+def _tie_rule_id() -> int:
+    import deepclr_b200
+    return deepclr_b200.FPS_TIE_RULES[deepclr_b200.get_fps_tie_rule()]
+
+
 def _call(name, *args):
     _lib.check(getattr(_lib.lib(), name)(*args, _lib.stream_ptr()), name)
 
@@ -18,13 +23,13 @@ def _call(name, *args):
 class FurthestPointSampling(Function):
     @staticmethod
     def forward(ctx, xyz: torch.Tensor, npoint: int) -> torch.Tensor:
-        """xyz (B, N, 3) -> (B, npoint) int32 indices; first index 0, ties -> lowest index."""
+        """xyz (B, N, 3) -> (B, npoint) int32 indices; first index 0, ties by deepclr_b200.get_fps_tie_rule()."""
         assert xyz.is_contiguous()
         _lib.require_cuda(xyz)
         B, N, _ = xyz.size()
         output = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
         with torch.cuda.device(xyz.device):
-            _call('dclr_fps', _lib.ptr(xyz), 3, B, N, npoint, _lib.ptr(output), None)
+            _call('dclr_fps', _lib.ptr(xyz), 3, B, N, npoint, _tie_rule_id(), _lib.ptr(output), None)
         ctx.mark_non_differentiable(output)
         return output
 

@@ -36,25 +36,25 @@ const char *dclr_last_error(void);
  * (src/sampling.cpp:36-46 -> src/sampling_gpu.cu:94-253) and, when new_xyz_out != NULL, the gather_operation that
  * always follows it (pointnet2_modules.py:32-35 -> sampling_gpu.cu:8-44).
  *   pts        [B, N, pt_stride] fp32, xyz in the first three floats of each point (pt_stride >= 3)
- *   idx_out    [B, npoint] int32; idx[.,0] = 0; equal maxima resolved by the tie rule below (default: lowest index)
+ *   tie_rule   how two points holding the running maximum with bit-equal fp32 distances are ordered (it happens about
+ *              once per 10^4 rounds on 16k-point scans):
+ *                DCLR_TIE_LOWEST_INDEX  lowest point index (the rule BASELINE.json states)
+ *                DCLR_TIE_REFERENCE     the reference kernel's own order, furthest_point_sampling_kernel
+ *                                       (sampling_gpu.cu:113-203): thread k mod T keeps its first strict maximum and
+ *                                       the shared-memory tree keeps the lower slot, i.e. the smallest bit-reversed
+ *                                       slot, then the smallest k; T = opt_n_threads(N) (cuda_utils.h:10-14).  With
+ *                                       it the indices are bit-identical to the reference kernel on every input.
+ *              There is no process-wide setting: the rule is an argument here and a property of a model handle
+ *              (dclr_model_set_fps_tie_rule, default DCLR_TIE_REFERENCE).
+ *   idx_out    [B, npoint] int32; idx[.,0] = 0
  *   new_xyz_out[B, npoint, 3] fp32 or NULL
  * The min-distance scratch the reference makes the caller allocate and fill with 1e10 (pointnet2_utils.py:26)
  * lives in registers here.  npoint > N is allowed (reference test tests/model/test_deepclr.py:10-25).
  */
-int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int32_t *idx_out, float *new_xyz_out,
-             void *stream);
-
-/*
- * FPS tie rule (process-wide; affects dclr_fps and the model entry points).  Two points can hold the running maximum
- * with bit-equal fp32 distances (about once per 10^4 rounds on 16k-point scans).
- *   0 (default) lowest point index            -- the rule BASELINE.json states
- *   1           the reference kernel's order  -- furthest_point_sampling_kernel (sampling_gpu.cu:113-203): thread
- *               k mod T keeps its first strict maximum and the shared-memory tree keeps the lower slot, i.e. the
- *               smallest bit-reversed slot, then the smallest k; T = opt_n_threads(N) (cuda_utils.h:10-14).
- *               With rule 1 the indices are bit-identical to the reference kernel on every input.
- */
-int dclr_set_fps_tie_rule(int rule);
-int dclr_get_fps_tie_rule(void);
+#define DCLR_TIE_LOWEST_INDEX 0
+#define DCLR_TIE_REFERENCE 1
+int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int tie_rule, int32_t *idx_out,
+             float *new_xyz_out, void *stream);
 
 /* out[b,c,j] = feat[b,c,idx[b,j]].  Replaces pointnet2_cuda.gather_points_wrapper (sampling.cpp:11-20). */
 int dclr_gather(const float *feat, const int32_t *idx, int B, int C, int N, int M, float *out, void *stream);
@@ -124,6 +124,9 @@ void dclr_model_destroy(dclr_model *m);
 /* numerics: 0 = fp32 SIMT everywhere (fp32-faithful); 1 = bf16, 2 = fp16 operands on the tcgen05 tensor cores
  * (fp32 accumulation in TMEM) for the flow-embedding and pose-head MLP stacks */
 int dclr_model_set_numerics(dclr_model *m, int mode);
+/* FPS tie order of this handle (see dclr_fps); default DCLR_TIE_REFERENCE = the reference kernel's own order. */
+int dclr_model_set_fps_tie_rule(dclr_model *m, int rule);
+int dclr_model_get_fps_tie_rule(const dclr_model *m);
 
 /*
  * Set abstraction (deepclr.py:510-521 -> :88-94 -> pointnet2_modules.py:19-55).

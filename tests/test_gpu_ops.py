@@ -86,7 +86,7 @@ def test_fps_point_stride_4_and_new_xyz():
     x = _t(pts)
     idx = torch.empty((2, 200), dtype=torch.int32, device=DEV)
     nx = torch.empty((2, 200, 3), dtype=torch.float32, device=DEV)
-    _lib.check(_lib.lib().dclr_fps(_lib.ptr(x), 4, 2, 3000, 200, _lib.ptr(idx), _lib.ptr(nx), _lib.stream_ptr()), 'fps')
+    _lib.check(_lib.lib().dclr_fps(_lib.ptr(x), 4, 2, 3000, 200, 0, _lib.ptr(idx), _lib.ptr(nx), _lib.stream_ptr()), 'fps')
     want = ops.fps_lowidx(pts, 200)
     assert np.array_equal(idx.cpu().numpy(), want)
     assert np.array_equal(nx.cpu().numpy(), np.stack([pts[b, want[b], :3] for b in range(2)]))

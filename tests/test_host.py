@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_argument_errors_are_reported_not_fatal():
     from deepclr_b200 import _lib
-    rc = _lib.lib().dclr_fps(None, 3, 1, 10, 4, None, None, None)
+    rc = _lib.lib().dclr_fps(None, 3, 1, 10, 4, 0, None, None, None)
     assert rc == -1 and b'null' in _lib.lib().dclr_last_error()
     rc = _lib.lib().dclr_knn(None, None, 1, 4, 4, 2, None, None, None)
     assert rc == -1
