@@ -625,7 +625,8 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
                       void *ws, cudaStream_t st, int *used, cudaEvent_t after_sort) {
     *used = 0;
     const int tie_ref = tie_rule == DCLR_TIE_REFERENCE;
-    static const int min_n = getenv("DCLR_FPS_BUCKET_MIN") ? atoi(getenv("DCLR_FPS_BUCKET_MIN")) : 8192;   // tuning knob; measured
+    const char *env_min = getenv("DCLR_FPS_BUCKET_MIN");          // tuning knob (read per call: tests switch it); measured
+    const int min_n = env_min ? atoi(env_min) : 8192;
     // per 8 clouds, bucketed | resident kernel: N = 4096 0.154 | 0.118 ms, 8192 0.306 | 0.295, 12288 0.416 | 0.727
     if (N <= min_n || N > 131072 || npoint < 2) return DCLR_OK;
     float4 *sorted = (float4 *)ws;
@@ -639,8 +640,9 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
         return rc;
     }
     // tuning knobs (tools/ab.sh): warps per cloud and samples per block-wide round (1 = the single-pick kernel)
-    static const int shape = getenv("DCLR_FPS_SHAPE") ? atoi(getenv("DCLR_FPS_SHAPE")) : 8;
-    static const int mp = getenv("DCLR_FPS_MP") ? atoi(getenv("DCLR_FPS_MP")) : 4;
+    const char *env_shape = getenv("DCLR_FPS_SHAPE"), *env_mp = getenv("DCLR_FPS_MP");
+    const int shape = env_shape ? atoi(env_shape) : 8;
+    const int mp = env_mp ? atoi(env_mp) : 4;
     if (N <= 4096) rc = launch_bucket_any<2>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);
     else if (N <= 8192) rc = launch_bucket_any<4>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);
     else rc = launch_bucket_any<8>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);

@@ -240,3 +240,34 @@ def test_device_to_matrix_and_kitti_errors_match_host(lt_name):
     # acos amplifies rounding near 0 / pi; these rotations are well away from both
     np.testing.assert_allclose(rot.cpu().numpy(), ref[:, 0], atol=1e-9)
     np.testing.assert_allclose(trans.cpu().numpy(), ref[:, 1], atol=1e-12)
+
+
+@pytest.mark.parametrize('shape,mp', [(8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 2), (16, 4), (16, 8), (32, 1)])
+def test_fps_multipick_variants_are_exact(p2, shape, mp, monkeypatch):
+    """Every warps-per-cloud x samples-per-round variant of the bucketed kernel (fps_bucket.cu; DCLR_FPS_SHAPE /
+    DCLR_FPS_MP are read per call) returns the indices of the serial algorithm (sampling_gpu.cu:113-208), under both tie
+    rules: KITTI-shaped scans, a cloud with a third of its points duplicated and an integer lattice (most rounds tie), a
+    ragged N, and npoint > N (all minima reach 0: the strict-> start of the reference, sampling_gpu.cu:119-137)."""
+    import deepclr_b200
+    from deepclr_b200 import synth
+    monkeypatch.setenv('DCLR_FPS_SHAPE', str(shape))
+    monkeypatch.setenv('DCLR_FPS_MP', str(mp))
+    rng = np.random.default_rng(7)
+    dup = rng.uniform(-40, 40, (2, 16384, 3)).astype(np.float32)
+    dup[:, rng.permutation(16384)[:5000]] = dup[:, rng.integers(0, 16384, 5000)]
+    cases = [(np.stack([synth.kitti_pair(300 + i, 16384)[i % 2][:, :3] for i in range(4)]), 1024),
+             (dup, 700),
+             (rng.integers(0, 14, (2, 12000, 3)).astype(np.float32), 400),
+             (rng.uniform(-30, 30, (3, 9001, 3)).astype(np.float32), 333),
+             (rng.uniform(-1, 1, (1, 8200, 3)).astype(np.float32), 8300)]
+    monkeypatch.setenv('DCLR_FPS_BUCKET_MIN', '2048')
+    cases.append((rng.uniform(-5, 5, (2, 3000, 3)).astype(np.float32), 256))      # the 4096- and 8192-record classes
+    cases.append((rng.uniform(-5, 5, (2, 6000, 3)).astype(np.float32), 256))
+    for xyz, npoint in cases:
+        want_low = ops.fps_lowidx(xyz, npoint)
+        got = p2.furthest_point_sample(_t(xyz), npoint).cpu().numpy()
+        assert np.array_equal(got, want_low), (xyz.shape, npoint, int((got != want_low).sum()))
+        deepclr_b200.set_fps_tie_rule('reference')
+        got = p2.furthest_point_sample(_t(xyz), npoint).cpu().numpy()
+        deepclr_b200.set_fps_tie_rule('lowest_index')
+        assert np.array_equal(got, ops.fps(xyz, npoint)), (xyz.shape, npoint)

@@ -32,14 +32,6 @@ def test_fps_equals_reference_kernel(p2, kind, B, N, npoint):
     assert np.array_equal(got, want)
 
 
-@pytest.fixture
-def reference_tie_rule():
-    import deepclr_b200
-    deepclr_b200.set_fps_tie_rule('reference')
-    yield
-    deepclr_b200.set_fps_tie_rule('lowest_index')
-
-
 @pytest.mark.parametrize('kind,B,N,npoint', [('lattice', 2, 700, 300), ('lattice', 2, 3000, 600), ('dup', 3, 1024, 512),
                                              ('dup', 2, 5000, 700), ('dup', 2, 16384, 1024), ('dup', 1, 20000, 300),
                                              ('kitti', 16, 16384, 1024), ('kitti', 2, 40000, 2500), ('dup', 1, 70001, 600),

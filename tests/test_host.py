@@ -34,6 +34,21 @@ def test_argument_errors_are_reported_not_fatal():
     assert rc == -1
 
 
+def test_package_default_tie_rule_is_the_reference_kernels():
+    """Out of the box FPS orders exact ties like the reference's furthest_point_sampling_kernel; the C ABI
+    has no process-wide setting any more."""
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, '-c', 'import deepclr_b200; print(deepclr_b200.get_fps_tie_rule())'],
+                         capture_output=True, text=True, cwd=ROOT).stdout.strip()
+    assert out == 'reference'
+    from deepclr_b200 import _lib
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    assert not hasattr(lib, 'dclr_set_fps_tie_rule') and hasattr(lib, 'dclr_model_set_fps_tie_rule')
+    assert _lib.lib().dclr_fps(ctypes.c_void_p(16), 3, 1, 10, 4, 7, ctypes.c_void_p(16), None, None) == -1
+    assert b'tie_rule' in _lib.lib().dclr_last_error()
+
+
 def test_no_cpu_route():
     from deepclr_b200.pointnet2 import furthest_point_sample
     with pytest.raises(RuntimeError, match='CUDA'):
