@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "ptx.cuh"
+#include "fps_bucket.cuh"
 #include <float.h>
 #include <limits.h>
 #include <stdlib.h>
@@ -132,47 +133,6 @@ fps_sort_kernel(const float *__restrict__ pts, int stride, int N, float4 *__rest
     }
 }
 
-// ---- packed fp32x2 helpers (FADD2 / FMUL2 / FFMA2: each half rounds exactly like the scalar op)
-__device__ __forceinline__ uint64_t fb_pack2(float lo, float hi) {
-    uint64_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ void fb_unpack2(uint64_t v, float &lo, float &hi) {
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ uint64_t fb_sub2(uint64_t a, uint64_t b) {
-    uint64_t r;
-    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ uint64_t fb_mul2(uint64_t a, uint64_t b) {
-    uint64_t r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ uint64_t fb_fma2(uint64_t a, uint64_t b, uint64_t c) {
-    uint64_t r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-__device__ __forceinline__ uint64_t fb_lds64(uint32_t addr) {
-    uint64_t r;
-    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(r) : "r"(addr));
-    return r;
-}
-__device__ __forceinline__ uint32_t fb_lds32(uint32_t addr) {
-    uint32_t r;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(addr));
-    return r;
-}
-
-// Tie order of the reference kernel for N > 1024 (1024-thread block, sampling_gpu.cu:113-203): thread tid = k & 1023
-// keeps its first strict maximum, the shared-memory tree keeps the LOWER slot on equal values at every level, so among
-// equal maxima the slot with the smallest bit-reversed tid wins, then the smallest k.  14 bits for N <= 16384.
-__device__ __forceinline__ uint32_t fb_rank16(int k) { return ((__brev((uint32_t)k & 1023u) >> 22) << 4) | ((uint32_t)k >> 10); }
-__device__ __forceinline__ int fb_unrank16(uint32_t r) { return (int)((__brev(r >> 4) >> 22) | ((r & 15u) << 10)); }
-
 #ifdef DCLR_TRACE
 __device__ long long g_fps_trace[4096];
 #define FTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && j >= 500 && j < 532) g_fps_trace[((j - 500) * 8 + warp) * 16 + (slot)] = clock64(); } while (0)
@@ -180,13 +140,9 @@ __device__ long long g_fps_trace[4096];
 extern "C" int dclr_debug_read_fps_trace(long long *dst, int n) {
     return cudaMemcpyFromSymbol(dst, g_fps_trace, sizeof(long long) * (n < 4096 ? n : 4096)) == cudaSuccess ? 0 : -1;
 }
-#define MTRACE(slot) do { if (blockIdx.x == 0 && lane == 0 && round >= 100 && round < 132) g_fps_trace[((round - 100) * 8 + (warp & 7)) * 16 + (slot)] = clock64(); } while (0)
-#define MTRACEV(slot, v) do { if (blockIdx.x == 0 && lane == 0 && round >= 100 && round < 132) g_fps_trace[((round - 100) * 8 + (warp & 7)) * 16 + (slot)] = (v); } while (0)
 #else
 #define FTRACE(slot) do { } while (0)
 #define FTRACEV(slot, v) do { } while (0)
-#define MTRACE(slot) do { } while (0)
-#define MTRACEV(slot, v) do { } while (0)
 #endif
 
 // NW warps, PP buckets per warp (bucket g = i * NW + warp); capacity CAP = 64 * NW * PP records.  Fewer, fatter warps
@@ -331,248 +287,6 @@ fps_bucket_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_
     }
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// Multi-pick rounds.  The kernel above emits ONE sample per block-wide round (skip test -> update -> 4 redux + barrier);
-// 1023 dependent rounds of ~960 cycles are its whole cost.  This variant emits up to MP samples per round, EXACTLY:
-// at the barrier every warp w publishes its best point (value v_w, tie key) and an upper bound u_w of every OTHER
-// running minimum in the warp.  Sort the NW warp winners c_0 >= c_1 >= ... by (value, tie key).  c_0 is the next sample.
-// c_r (r >= 1) is provably the sample after c_0 .. c_{r-1} when for every l < r
-//      d(c_r, c_l) >= t[c_r]      (its minimum is untouched by the picks before it: min(d, t) == t) and
-//      u_{warp(c_l)} <  t[c_r]    (nothing that is left in an earlier winner's warp can overtake it) and t[c_r] > 0:
-// every other point's minimum can only fall, the points of warps ranked after c_r were <= t[c_r] with a later tie key
-// already, the remaining points of c_r's own warp likewise, those of the earlier winners' warps are < t[c_r] by u, and
-// the earlier picks themselves drop to 0.  The accepted prefix (1 .. MP samples) is then applied in ONE update pass
-// (t = min(t, d_0, .., d_{MP-1}), min-updates commute; unused pick slots sit at 1e18 and change nothing).
-// tools/fps_multipick_sim.py: 1023 serial rounds become ~565 (MP=2), ~427 (MP=3), ~380 (MP=4) on KITTI-shaped scans.
-// Per bucket the kernel additionally keeps bm2 = upper bound of the second-largest minimum (one more redux per update).
-template <int NW, int PP, int MP>
-__global__ void __launch_bounds__(NW * 32, 1)
-fps_bucket_mp_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_ref, int32_t *__restrict__ idx_out,
-                     float *__restrict__ new_xyz_out) {
-    extern __shared__ __align__(16) float smem[];
-    constexpr int CAP = 64 * NW * PP;
-    constexpr int T = NW * 32;
-    constexpr int WSTRIDE = 64 * NW;
-    constexpr int NPAIR = MP * (MP - 1) / 2;
-    static_assert(PP <= 32 && NW <= 32 && MP >= 1 && MP <= NW && NPAIR <= 32, "lane <-> bucket / warp slot / candidate pair");
-    float *s_x = smem, *s_y = smem + CAP, *s_z = smem + 2 * CAP;
-    uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem + 3 * CAP);
-    int4 *s_slot = reinterpret_cast<int4 *>(s_idx + CAP);                        // [2][32] (max bits, key, bound, -)
-    int4 *s_cand = s_slot + 64;                                                  // [NW][MP] sorted winners, per warp
-    int *s_start = reinterpret_cast<int *>(s_cand + NW * MP);
-
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    sorted += (size_t)b * N;
-    idx_out += (size_t)b * npoint;
-    if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
-
-    for (int k = tid; k < CAP; k += T) {
-        if (k < N) {
-            const float4 r = __ldg(sorted + k);
-            const int oi = __float_as_int(r.w);
-            s_x[k] = r.x; s_y[k] = r.y; s_z[k] = r.z;
-            s_idx[k] = (uint16_t)(tie_ref ? fb_rank16(oi) : oi);
-            if (oi == 0) *s_start = k;
-        } else {
-            s_x[k] = 0.f; s_y[k] = 0.f; s_z[k] = 0.f; s_idx[k] = 0xffffu;
-        }
-    }
-    __syncthreads();
-
-    float tl[PP], th[PP];
-    float blx = 0.f, bly = 0.f, blz = 0.f, bhx = 0.f, bhy = 0.f, bhz = 0.f, bm = -1.0f, bm2 = -1.0f;
-    uint32_t bkey = 0xffffffffu;
-    const uint32_t rec0 = (uint32_t)(64 * warp + 2 * lane);
-    const uint32_t ax = ptx::smem_u32(s_x) + rec0 * 4, ay = ptx::smem_u32(s_y) + rec0 * 4,
-                   az = ptx::smem_u32(s_z) + rec0 * 4, ai = ptx::smem_u32(s_idx) + rec0 * 2;
-#pragma unroll
-    for (int i = 0; i < PP; ++i) {
-        const int p = (int)rec0 + WSTRIDE * i;
-        const bool v0 = p < N, v1 = p + 1 < N;
-        tl[i] = v0 ? 1e10f : -1.0f;
-        th[i] = v1 ? 1e10f : -1.0f;
-        float lo[3], hi[3];
-        const float c0[3] = {s_x[p], s_y[p], s_z[p]}, c1[3] = {s_x[p + 1], s_y[p + 1], s_z[p + 1]};
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            lo[a] = fminf(v0 ? c0[a] : FLT_MAX, v1 ? c1[a] : FLT_MAX);
-            hi[a] = fmaxf(v0 ? c0[a] : -FLT_MAX, v1 ? c1[a] : -FLT_MAX);
-#pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) {
-                lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], d));
-                hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], d));
-            }
-        }
-        const bool any = __any_sync(0xffffffffu, v0);
-        if (lane == i) {
-            blx = lo[0]; bly = lo[1]; blz = lo[2]; bhx = hi[0]; bhy = hi[1]; bhz = hi[2];
-            bm = any ? 1e10f : -1.0f;          // 1e10 forces the first update; key and bm2 are set there
-            bm2 = bm;
-        }
-    }
-
-    // candidate pair (pl, pr), pl < pr, tested by this lane: pair index p = pr (pr - 1) / 2 + pl
-    int pl = 0, pr = 1;
-#pragma unroll
-    for (int r = 1; r < MP; ++r)
-        if (lane >= r * (r - 1) / 2) { pr = r; pl = lane - r * (r - 1) / 2; }
-    const bool pair_lane = lane < NPAIR;
-
-    int ppos[MP];                                 // positions (sorted order) of the picks being applied this round
-#pragma unroll
-    for (int q = 0; q < MP; ++q) ppos[q] = 0;
-    ppos[0] = *s_start;
-    int npk = 1, done = 1;                        // done = samples selected so far (the picks included)
-    int ewm = INT_MIN, ew2 = INT_MIN;             // this warp's published entry (recomputed only when a bucket changed)
-    uint32_t ewk = 0xffffffffu;
-    bool efresh = false;
-    if (tid == 0) idx_out[0] = 0;
-    for (int round = 0;; ++round) {
-        float px[MP], py[MP], pz[MP];
-#pragma unroll
-        for (int q = 0; q < MP; ++q) {
-            const bool on = q < npk;
-            px[q] = on ? s_x[ppos[q]] : 1e18f; py[q] = on ? s_y[ppos[q]] : 1e18f; pz[q] = on ? s_z[ppos[q]] : 1e18f;
-        }
-        if (new_xyz_out) {
-#pragma unroll
-            for (int q = 0; q < MP; ++q)
-                if (tid == q && q < npk) {
-                    float *o = new_xyz_out + (size_t)(done - npk + q) * 3;
-                    o[0] = px[q]; o[1] = py[q]; o[2] = pz[q];
-                }
-        }
-        if (done >= npoint) break;
-        MTRACE(0);
-        MTRACEV(7, npk);
-        // ---- which of this warp's buckets can change?  (lane i tests bucket i against every pick)
-        bool need = false;
-        if (lane < PP) {
-#pragma unroll
-            for (int q = 0; q < MP; ++q) {
-                const float ex = fmaxf(fmaxf(blx - px[q], px[q] - bhx), 0.f), ey = fmaxf(fmaxf(bly - py[q], py[q] - bhy), 0.f),
-                            ez = fmaxf(fmaxf(blz - pz[q], pz[q] - bhz), 0.f);
-                need |= (ex * ex + ey * ey + ez * ez) * 0.9999f < bm;
-            }
-        }
-        const unsigned mask = __ballot_sync(0xffffffffu, need);
-        MTRACE(1);
-        MTRACEV(6, __popc(mask));
-        if (mask) {
-            uint64_t xo[MP], yo[MP], zo[MP];
-#pragma unroll
-            for (int q = 0; q < MP; ++q) { xo[q] = fb_pack2(px[q], px[q]); yo[q] = fb_pack2(py[q], py[q]); zo[q] = fb_pack2(pz[q], pz[q]); }
-            auto upd = [&](const int i) {
-                const uint64_t X = fb_lds64(ax + i * (WSTRIDE * 4)), Y = fb_lds64(ay + i * (WSTRIDE * 4)),
-                               Z = fb_lds64(az + i * (WSTRIDE * 4));
-                const uint32_t id2 = fb_lds32(ai + i * (WSTRIDE * 2));
-                float nl = tl[i], nh = th[i];
-#pragma unroll
-                for (int q = 0; q < MP; ++q) {
-                    const uint64_t dx = fb_sub2(X, xo[q]), dy = fb_sub2(Y, yo[q]), dz = fb_sub2(Z, zo[q]);
-                    const uint64_t d2 = fb_fma2(dz, dz, fb_fma2(dx, dx, fb_mul2(dy, dy)));
-                    float dl, dh;
-                    fb_unpack2(d2, dl, dh);
-                    nl = fminf(dl, nl);
-                    nh = fminf(dh, nh);
-                }
-                tl[i] = nl; th[i] = nh;
-                const int mx = __float_as_int(fmaxf(nl, nh)), mn = __float_as_int(fminf(nl, nh));
-                const int bmx = __reduce_max_sync(0xffffffffu, mx);
-                const uint32_t p = rec0 + (uint32_t)WSTRIDE * i;
-                const uint32_t klo = __float_as_int(nl) == bmx ? ((id2 & 0xffffu) << 16 | p) : 0xffffffffu;
-                const uint32_t khi = __float_as_int(nh) == bmx ? ((id2 >> 16) << 16 | (p + 1)) : 0xffffffffu;
-                const bool holder = mx == bmx;
-                const uint32_t kmin = __reduce_min_sync(0xffffffffu, min(klo, khi));
-                // second-largest minimum of the bucket (upper bound): the holder lane contributes its other point;
-                // two holder lanes (or both points of one lane) => the maximum itself
-                int b2 = __reduce_max_sync(0xffffffffu, holder ? mn : mx);
-                if (__popc(__ballot_sync(0xffffffffu, holder)) > 1) b2 = bmx;
-                if (lane == i) { bm = __int_as_float(bmx); bkey = kmin; bm2 = __int_as_float(b2); }
-            };
-            constexpr int GR = PP < 8 ? PP : 8;
-#pragma unroll
-            for (int q = 0; q < PP / GR; ++q) {
-                if (PP > 8 && ((mask >> (q * GR)) & 0xffu) == 0) continue;
-#pragma unroll
-                for (int r = 0; r < GR; ++r)
-                    if ((mask >> (q * GR + r)) & 1u) upd(q * GR + r);
-            }
-        }
-        MTRACE(2);
-        // ---- this warp's entry: best point, its key, bound of everything else in the warp
-        if (mask || !efresh) {
-            const int mybits = lane < PP ? __float_as_int(bm) : INT_MIN;
-            ewm = __reduce_max_sync(0xffffffffu, mybits);
-            const bool iswin = lane < PP && mybits == ewm;
-            ewk = __reduce_min_sync(0xffffffffu, iswin ? bkey : 0xffffffffu);
-            ew2 = __reduce_max_sync(0xffffffffu, iswin ? __float_as_int(bm2) : mybits);
-            if (__popc(__ballot_sync(0xffffffffu, iswin)) > 1) ew2 = ewm;
-            efresh = true;
-        }
-        int4 *slot = s_slot + (round & 1) * 32;
-        if (lane == 0) slot[warp] = make_int4(ewm, (int)ewk, ew2, 0);
-        MTRACE(3);
-        __syncthreads();
-        // ---- every warp ranks the NW entries (value desc, key asc, warp asc) and lays the first MP out in order
-        {
-            const int4 e = lane < NW ? slot[lane] : make_int4(INT_MIN, -1, INT_MIN, 0);
-            int rank = 0;
-#pragma unroll
-            for (int a = 0; a < NW; ++a) {
-                const int2 o = *reinterpret_cast<const int2 *>(slot + a);
-                rank += (o.x > e.x) || (o.x == e.x && ((uint32_t)o.y < (uint32_t)e.y || (o.y == e.y && a < lane)));
-            }
-            if (lane < NW && rank < MP) s_cand[warp * MP + rank] = e;
-        }
-        __syncwarp();
-        int cv[MP], cw[MP];
-        uint32_t ck[MP];
-#pragma unroll
-        for (int q = 0; q < MP; ++q) {
-            const int4 c = s_cand[warp * MP + q];
-            cv[q] = c.x; ck[q] = (uint32_t)c.y; cw[q] = c.z;
-            ppos[q] = (int)(ck[q] & 0xffffu);
-        }
-        int take = 1;
-        if (MP > 1) {
-            float qx[MP], qy[MP], qz[MP];
-#pragma unroll
-            for (int q = 0; q < MP; ++q) {
-                const bool real = cv[q] > 0;                 // (an invalid winner has key 0xffffffff: no position)
-                qx[q] = real ? s_x[ppos[q]] : 0.f; qy[q] = real ? s_y[ppos[q]] : 0.f; qz[q] = real ? s_z[ppos[q]] : 0.f;
-            }
-            // lane p tests pair (pl, pr): the update's own arithmetic, point c_pr against sample c_pl
-            float lx = qx[0], ly = qy[0], lz = qz[0], rx = qx[MP - 1], ry = qy[MP - 1], rz = qz[MP - 1];
-            int lw = cw[0], rv = cv[MP - 1];
-#pragma unroll
-            for (int q = 1; q < MP - 1; ++q) {
-                if (pl == q) { lx = qx[q]; ly = qy[q]; lz = qz[q]; lw = cw[q]; }
-            }
-#pragma unroll
-            for (int q = 1; q < MP - 1; ++q) {
-                if (pr == q) { rx = qx[q]; ry = qy[q]; rz = qz[q]; rv = cv[q]; }
-            }
-            const float dx = rx - lx, dy = ry - ly, dz = rz - lz;
-            const float d = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-            const bool ok = pair_lane && rv > 0 && d >= __int_as_float(rv) && lw < rv;
-            const unsigned okm = __ballot_sync(0xffffffffu, ok);
-#pragma unroll
-            for (int r = 1; r < MP; ++r) {
-                const unsigned want = ((1u << r) - 1u) << (r * (r - 1) / 2);
-                if (take == r && (okm & want) == want) take = r + 1;
-            }
-            take = min(take, npoint - done);
-        }
-        npk = take;
-        MTRACEV(4, clock64() + (npk & 0));
-#pragma unroll
-        for (int q = 0; q < MP; ++q)
-            if (tid == q && q < npk) idx_out[done + q] = tie_ref ? fb_unrank16(ck[q] >> 16) : (int)(ck[q] >> 16);
-        done += npk;
-    }
-}
-
 // records [B*N] float4 (+ running minima [B*N] fp32 for the L2-resident variant, N > 16384)
 size_t fps_bucket_workspace_bytes(int B, int N) {
     return (size_t)B * N * (sizeof(float4) + (N > 16384 ? sizeof(float) : 0)) + 256;
@@ -589,35 +303,13 @@ static int launch_bucket(const float4 *sorted, int B, int N, int npoint, int tie
     return DCLR_OK;
 }
 
-template <int NW, int PP, int MP>
-static int launch_bucket_mp(const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
-                            cudaStream_t st) {
-    const size_t smem = (size_t)64 * NW * PP * 14 + 64 * sizeof(int4) + (size_t)NW * MP * sizeof(int4) + 16;
-    auto kern = fps_bucket_mp_kernel<NW, PP, MP>;
-    DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<B, NW * 32, smem, st>>>(sorted, N, npoint, tie_ref, idx, nx);
-    DCLR_LAUNCH_CHECK("fps_bucket_mp_kernel");
-    return DCLR_OK;
-}
-
-// CAPK = capacity / 2048 records; warps x buckets per warp = CAPK * 32; mp = samples per block-wide round
+// CAPK = capacity / 2048 records; warps x buckets per warp = CAPK * 32
 template <int CAPK>
-static int launch_bucket_any(int nw, int mp, const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx,
-                             float *nx, cudaStream_t st) {
-    if (mp <= 1) {
-        if (nw == 32) return launch_bucket<32, CAPK>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        if (nw == 16) return launch_bucket<16, CAPK * 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        return launch_bucket<8, CAPK * 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    }
-    if (nw == 16) {
-        if (mp == 2) return launch_bucket_mp<16, CAPK * 2, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        if (mp <= 4) return launch_bucket_mp<16, CAPK * 2, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        return launch_bucket_mp<16, CAPK * 2, 8>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    }
-    if (mp == 2) return launch_bucket_mp<8, CAPK * 4, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    if (mp == 3) return launch_bucket_mp<8, CAPK * 4, 3>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    if (mp <= 4) return launch_bucket_mp<8, CAPK * 4, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    return launch_bucket_mp<8, CAPK * 4, 6>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+static int launch_bucket_any(int nw, const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
+                             cudaStream_t st) {
+    if (nw == 32) return launch_bucket<32, CAPK>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    if (nw == 16) return launch_bucket<16, CAPK * 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
+    return launch_bucket<8, CAPK * 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
 }
 
 // *used = 0 when the shape is not handled (caller falls back to fps_launch)
@@ -639,13 +331,15 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
         if (rc == DCLR_OK) *used = 1;
         return rc;
     }
-    // tuning knobs (tools/ab.sh): warps per cloud and samples per block-wide round (1 = the single-pick kernel)
+    // tuning knobs, read per call (tools/fps_ab.py, tests): DCLR_FPS_SHAPE = warps per cloud; DCLR_FPS_MP = samples per
+    // block-wide round at most; DCLR_FPS_MP=0 = the register-resident single-pick kernel of this file
     const char *env_shape = getenv("DCLR_FPS_SHAPE"), *env_mp = getenv("DCLR_FPS_MP");
     const int shape = env_shape ? atoi(env_shape) : 8;
     const int mp = env_mp ? atoi(env_mp) : 4;
-    if (N <= 4096) rc = launch_bucket_any<2>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);
-    else if (N <= 8192) rc = launch_bucket_any<4>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);
-    else rc = launch_bucket_any<8>(shape, mp, sorted, B, N, npoint, tie_ref, idx, nx, st);
+    if (mp >= 1) rc = fps_tmem_launch(sorted, B, N, npoint, tie_ref, shape, mp, idx, nx, st);
+    else if (N <= 4096) rc = launch_bucket_any<2>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else if (N <= 8192) rc = launch_bucket_any<4>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);
+    else rc = launch_bucket_any<8>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);
     if (rc == DCLR_OK) *used = 1;
     return rc;
 }

@@ -16,6 +16,9 @@ int fps_launch(const float *pts, int stride, int B, int N, int npoint, int tie_r
 size_t fps_bucket_workspace_bytes(int B, int N);
 int fps_bucket_l2_launch(const float4 *sorted, float *tmin, int B, int N, int npoint, int tieL, int32_t *idx, float *nx,
                          cudaStream_t st);
+// fps_tmem.cu: running minima in tensor memory, up to mp samples per round; sorted = fps_sort_kernel's records, N <= 16384
+int fps_tmem_launch(const float4 *sorted, int B, int N, int npoint, int tie_ref, int nw, int mp, int32_t *idx, float *nx,
+                    cudaStream_t st);
 // after_sort (optional) is recorded on st between the sort and the sampling kernel
 int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int tie_rule, int32_t *idx, float *new_xyz,
                       void *ws, cudaStream_t st, int *used, cudaEvent_t after_sort = nullptr);

@@ -19,12 +19,12 @@ for _ in range(3):
     pu.furthest_point_sample(xyz, 1024)
 torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 4096)()
-fn = _lib.lib().dclr_debug_read_fps_trace
+mp = int(os.environ.get('DCLR_FPS_MP', '4'))
+fn = _lib.lib().dclr_debug_read_fps_trace if mp == 0 else _lib.lib().dclr_debug_read_fps_trace_tm
 fn.argtypes = [ctypes.c_void_p, ctypes.c_int]
 assert fn(buf, 4096) == 0
 t = np.array(buf[:4096], dtype=np.int64).reshape(32, 8, 16)
-mp = int(os.environ.get('DCLR_FPS_MP', '4'))
-if mp == 1:
+if mp == 0:
     print('round: per-warp [updates] | warp0: test, upd, reduce, barrier+final | round length (warp0 start to next start)')
     for r in range(31):
         w = t[r]

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q -k "fps" > gpurun_out/r2a_pytest_fps.log 2>&1; tail -3 gpurun_out/r2a_pytest_fps.log
 python tools/fps_ab.py > gpurun_out/r2a_fps_ab.jsonl 2> gpurun_out/r2a_fps_ab.err; tail -40 gpurun_out/r2a_fps_ab.jsonl
-for v in "8 4" "8 2" "16 4" "8 1"; do set -- $v
+for v in "8 4" "8 2" "16 4" "8 1" "8 0"; do set -- $v
   DCLR_LIB=$PWD/deepclr_b200/lib_trace.so DCLR_FPS_SHAPE=$1 DCLR_FPS_MP=$2 python tools/fps_trace.py > gpurun_out/r2a_fps_trace_$1x$2.txt 2>&1
   tail -4 gpurun_out/r2a_fps_trace_$1x$2.txt
 done
