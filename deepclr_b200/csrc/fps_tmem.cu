@@ -64,10 +64,11 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     static_assert((TCOLS & (TCOLS - 1)) == 0 && TCOLS <= 512, "TMEM columns: power of two");
     float *s_x = smem, *s_y = smem + CAP, *s_z = smem + 2 * CAP;
     uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem + 3 * CAP);             // tie rank of the original index
-    int4 *s_slot = reinterpret_cast<int4 *>(s_idx + CAP);                        // [2][32] (value^sign, ~key, bound, -)
-    int4 *s_cand = s_slot + 64;                                                  // [NW][MP] sorted winners, per warp
-    int *s_start = reinterpret_cast<int *>(s_cand + NW * MP);
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_start + 1);
+    // warp entries [2][NW] x {value^sign, ~key, bound, -}, {x, y, z, -}; per warp the first MP winners in order [NW][MP] x same
+    int4 *s_slot = reinterpret_cast<int4 *>(s_idx + CAP);
+    int4 *s_cand = s_slot + 4 * NW;
+    int *s_start = reinterpret_cast<int *>(s_cand);                              // (both only live before the first round)
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_cand) + 1;
 
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     sorted += (size_t)b * N;
@@ -90,7 +91,8 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     __syncthreads();
     ptx::tc_fence_after();
     // this thread's t of bucket i: TMEM lane (32 (warp % 4) + lane), columns tcol + 2 i, + 1
-    const uint32_t tcol = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * 2 * PP);
+    const uint32_t tmem_base = *s_tmem;
+    const uint32_t tcol = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * 2 * PP);
 
     // ---- per-bucket metadata (lane i < PP <-> the warp's i-th bucket): box, max t, key of the max, second max (bound)
     float blx = 0.f, bly = 0.f, blz = 0.f, bhx = 0.f, bhy = 0.f, bhz = 0.f, bm = -1.0f, bm2 = -1.0f;
@@ -130,43 +132,36 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     for (int r = 1; r < MP; ++r)
         if (lane >= r * (r - 1) / 2) { pr = r; pl = lane - r * (r - 1) / 2; }
     const bool pair_lane = lane < NPAIR;
+    const int4 *cand = s_cand + warp * (2 * MP);  // this warp's copy of the first MP winners in order: {hi, lo, bound, -}, {x, y, z, -}
 
-    int ppos[MP];                                 // positions (sorted order) of the picks being applied this round
+    // picks applied in the coming round: coordinates in registers (unused slots far away: they change nothing)
+    float px[MP], py[MP], pz[MP];
 #pragma unroll
-    for (int q = 0; q < MP; ++q) ppos[q] = 0;
-    ppos[0] = *s_start;
-    int npk = 1, done = 1;                        // done = samples selected so far (the picks included)
+    for (int q = 0; q < MP; ++q) { px[q] = 1e18f; py[q] = 1e18f; pz[q] = 1e18f; }
+    {
+        const int st = *s_start;
+        px[0] = s_x[st]; py[0] = s_y[st]; pz[0] = s_z[st];
+        if (tid == 0) {
+            idx_out[0] = 0;
+            if (new_xyz_out) { new_xyz_out[0] = px[0]; new_xyz_out[1] = py[0]; new_xyz_out[2] = pz[0]; }
+        }
+    }
+    int done = 1;                                 // samples selected (and written) so far
     uint32_t ehi = 0u, elo = 0u;                  // this warp's published entry (recomputed only when a bucket changed)
     int ew2 = INT_MIN;
+    float ex = 0.f, ey = 0.f, ez = 0.f;
     bool efresh = false;
-    if (tid == 0) idx_out[0] = 0;
-    for (int round = 0;; ++round) {
-        float px[MP], py[MP], pz[MP];
-#pragma unroll
-        for (int q = 0; q < MP; ++q) {
-            const bool on = q < npk;
-            px[q] = on ? s_x[ppos[q]] : 1e18f; py[q] = on ? s_y[ppos[q]] : 1e18f; pz[q] = on ? s_z[ppos[q]] : 1e18f;
-        }
-        if (new_xyz_out) {
-#pragma unroll
-            for (int q = 0; q < MP; ++q)
-                if (tid == q && q < npk) {
-                    float *o = new_xyz_out + (size_t)(done - npk + q) * 3;
-                    o[0] = px[q]; o[1] = py[q]; o[2] = pz[q];
-                }
-        }
-        if (done >= npoint) break;
+    for (int round = 0; done < npoint; ++round) {
         MTRACE(0);
-        MTRACEV(7, npk);
         // ---- which of this warp's buckets can change?  (lane i tests bucket i against every pick; branch-free)
         unsigned need = 0u;
 #pragma unroll
         for (int q = 0; q < MP; ++q) {
-            const float ex = fmax3(blx - px[q], px[q] - bhx, 0.f), ey = fmax3(bly - py[q], py[q] - bhy, 0.f),
-                        ez = fmax3(blz - pz[q], pz[q] - bhz, 0.f);
-            need |= (unsigned)((ex * ex + ey * ey + ez * ez) * 0.9999f < bm);
+            const float dx = fmax3(blx - px[q], px[q] - bhx, 0.f), dy = fmax3(bly - py[q], py[q] - bhy, 0.f),
+                        dz = fmax3(blz - pz[q], pz[q] - bhz, 0.f);
+            need |= (unsigned)((dx * dx + dy * dy + dz * dz) * 0.9999f < bm);
         }
-        unsigned mask = __ballot_sync(0xffffffffu, need != 0u && lane < PP);
+        unsigned mask = __ballot_sync(0xffffffffu, need != 0u);     // (lanes >= PP keep bm = -1: never set)
         MTRACE(1);
         MTRACEV(6, __popc(mask));
         const bool touched = mask != 0u;
@@ -239,7 +234,7 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
             }
         }
         MTRACE(2);
-        // ---- this warp's entry: best point, its key, bound of everything else in the warp
+        // ---- this warp's entry: best point (value, key, coordinates), bound of everything else in the warp
         if (touched || !efresh) {
             const int mybits = lane < PP ? __float_as_int(bm) : INT_MIN;
             const int ewm = __reduce_max_sync(0xffffffffu, mybits);
@@ -249,57 +244,47 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
             if (__popc(__ballot_sync(0xffffffffu, iswin)) > 1) ew2 = ewm;
             ehi = (uint32_t)ewm ^ 0x80000000u;            // larger = better, as one unsigned 64-bit number (ehi:elo)
             elo = ~ewk;
+            const int wp = ewm >= 0 ? (int)(ewk & 0xffffu) : 0;     // (an invalid winner's key holds no position)
+            ex = s_x[wp]; ey = s_y[wp]; ez = s_z[wp];
             efresh = true;
         }
-        int4 *slot = s_slot + (round & 1) * 32;
-        if (lane == 0) slot[warp] = make_int4((int)ehi, (int)elo, ew2, 0);
+        int4 *slot = s_slot + (round & 1) * (2 * NW);
+        if (lane == 0) {
+            slot[2 * warp] = make_int4((int)ehi, (int)elo, ew2, 0);
+            slot[2 * warp + 1] = make_int4(__float_as_int(ex), __float_as_int(ey), __float_as_int(ez), 0);
+        }
         MTRACE(3);
         __syncthreads();
         // ---- every warp ranks the NW entries (value desc, key asc; keys are distinct) and lays the first MP out in order
         {
-            const int4 e = slot[lane < NW ? lane : 0];
-            const uint64_t me = ((uint64_t)(uint32_t)e.x << 32) | (uint32_t)e.y;
-            int rank = 0;
+            const int me_i = lane < NW ? lane : 0;
+            const int4 eA = slot[2 * me_i], eB = slot[2 * me_i + 1];
+            const uint64_t me = ((uint64_t)(uint32_t)eA.x << 32) | (uint32_t)eA.y;
+            int c[NW];
 #pragma unroll
             for (int a = 0; a < NW; ++a) {
-                const uint2 o = *reinterpret_cast<const uint2 *>(slot + a);
-                rank += (int)((((uint64_t)o.x << 32) | o.y) > me);
+                const uint2 o = *reinterpret_cast<const uint2 *>(slot + 2 * a);
+                c[a] = (int)((((uint64_t)o.x << 32) | o.y) > me);
             }
-            if (lane < NW && rank < MP) s_cand[warp * MP + rank] = e;
+#pragma unroll
+            for (int s = 1; s < NW; s <<= 1)
+#pragma unroll
+                for (int a = 0; a + s < NW; a += 2 * s) c[a] += c[a + s];
+            if (lane < NW && c[0] < MP) {
+                s_cand[warp * (2 * MP) + 2 * c[0]] = eA;
+                s_cand[warp * (2 * MP) + 2 * c[0] + 1] = eB;
+            }
         }
         __syncwarp();
-        int cv[MP], cw[MP];
-        uint32_t ck[MP];
-#pragma unroll
-        for (int q = 0; q < MP; ++q) {
-            const int4 c = s_cand[warp * MP + q];
-            cv[q] = (int)((uint32_t)c.x ^ 0x80000000u); ck[q] = ~(uint32_t)c.y; cw[q] = c.z;
-            ppos[q] = (int)(ck[q] & 0xffffu);
-        }
         int take = 1;
         if (MP > 1) {
-            float qx[MP], qy[MP], qz[MP];
-#pragma unroll
-            for (int q = 0; q < MP; ++q) {
-                const int pp = cv[q] > 0 ? ppos[q] : 0;      // (an invalid winner's key holds no position)
-                qx[q] = s_x[pp]; qy[q] = s_y[pp]; qz[q] = s_z[pp];
-            }
             // lane p tests pair (pl, pr): the update's own arithmetic, point c_pr against sample c_pl
-            float lx = qx[0], ly = qy[0], lz = qz[0], rx = qx[MP - 1], ry = qy[MP - 1], rz = qz[MP - 1];
-            int lw = cw[0], rv = cv[MP - 1];
-#pragma unroll
-            for (int q = 1; q < MP - 1; ++q) {
-                const bool s = pl == q;
-                lx = s ? qx[q] : lx; ly = s ? qy[q] : ly; lz = s ? qz[q] : lz; lw = s ? cw[q] : lw;
-            }
-#pragma unroll
-            for (int q = 1; q < MP - 1; ++q) {
-                const bool s = pr == q;
-                rx = s ? qx[q] : rx; ry = s ? qy[q] : ry; rz = s ? qz[q] : rz; rv = s ? cv[q] : rv;
-            }
-            const float dx = rx - lx, dy = ry - ly, dz = rz - lz;
+            const int4 lA = cand[2 * pl], lB = cand[2 * pl + 1], rA = cand[2 * pr], rB = cand[2 * pr + 1];
+            const int rv = (int)((uint32_t)rA.x ^ 0x80000000u);
+            const float dx = __int_as_float(rB.x) - __int_as_float(lB.x), dy = __int_as_float(rB.y) - __int_as_float(lB.y),
+                        dz = __int_as_float(rB.z) - __int_as_float(lB.z);
             const float d = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-            const bool ok = pair_lane & (rv > 0) & (d >= __int_as_float(rv)) & (lw < rv);
+            const bool ok = pair_lane & (rv > 0) & (d >= __int_as_float(rv)) & (lA.z < rv);
             const unsigned okm = __ballot_sync(0xffffffffu, ok);
 #pragma unroll
             for (int r = 1; r < MP; ++r) {
@@ -308,22 +293,38 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
             }
             take = min(take, npoint - done);
         }
-        npk = take;
-        MTRACEV(4, clock64() + (npk & 0));
+        // next round's picks (uniform) ...
 #pragma unroll
-        for (int q = 0; q < MP; ++q)
-            if (tid == q && q < npk) idx_out[done + q] = tie_ref ? fb_unrank16(ck[q] >> 16) : (int)(ck[q] >> 16);
-        done += npk;
+        for (int q = 0; q < MP; ++q) {
+            const int4 cB = cand[2 * q + 1];
+            const bool on = q < take;
+            px[q] = on ? __int_as_float(cB.x) : 1e18f; py[q] = on ? __int_as_float(cB.y) : 1e18f;
+            pz[q] = on ? __int_as_float(cB.z) : 1e18f;
+        }
+        MTRACEV(4, clock64() + (take & 0));
+        MTRACEV(7, take);
+        // ... and their record: lane q of warp 0 writes sample done + q
+        if (tid < take) {
+            const int4 cA = cand[2 * tid], cB = cand[2 * tid + 1];
+            const uint32_t key = ~(uint32_t)cA.y;
+            idx_out[done + tid] = tie_ref ? fb_unrank16(key >> 16) : (int)(key >> 16);
+            if (new_xyz_out) {
+                float *o = new_xyz_out + (size_t)(done + tid) * 3;
+                o[0] = __int_as_float(cB.x); o[1] = __int_as_float(cB.y); o[2] = __int_as_float(cB.z);
+            }
+        }
+        done += take;
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 0) ptx::tmem_dealloc(*s_tmem, TCOLS);
+    if (warp == 0) ptx::tmem_dealloc(tmem_base, TCOLS);
 }
 
 template <int NW, int PP, int MP>
 static int launch_tmem(const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
                        cudaStream_t st) {
-    const size_t smem = (size_t)64 * NW * PP * 14 + 64 * sizeof(int4) + (size_t)NW * MP * sizeof(int4) + 16;
+    const size_t smem = (size_t)64 * NW * PP * 14 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4);
+    static_assert((size_t)64 * NW * PP * 14 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4) <= 232448, "shared memory");
     auto kern = fps_tmem_kernel<NW, PP, MP>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<B, NW * 32, smem, st>>>(sorted, N, npoint, tie_ref, idx, nx);
@@ -338,12 +339,7 @@ static int launch_tmem_any(int nw, int mp, const float4 *sorted, int B, int N, i
     if (nw == 16) {
         if (mp <= 1) return launch_tmem<16, CAPK * 2, 1>(sorted, B, N, npoint, tie_ref, idx, nx, st);
         if (mp == 2) return launch_tmem<16, CAPK * 2, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        if (mp <= 4) return launch_tmem<16, CAPK * 2, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        return launch_tmem<16, CAPK * 2, 6>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-    }
-    if (nw == 32) {
-        if (mp <= 1) return launch_tmem<32, CAPK, 1>(sorted, B, N, npoint, tie_ref, idx, nx, st);
-        return launch_tmem<32, CAPK, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);     // (shared memory: 32 x MP entries)
+        return launch_tmem<16, CAPK * 2, 4>(sorted, B, N, npoint, tie_ref, idx, nx, st);      // (shared memory: 16 x MP entries)
     }
     if (mp <= 1) return launch_tmem<8, CAPK * 4, 1>(sorted, B, N, npoint, tie_ref, idx, nx, st);
     if (mp == 2) return launch_tmem<8, CAPK * 4, 2>(sorted, B, N, npoint, tie_ref, idx, nx, st);

@@ -242,7 +242,7 @@ def test_device_to_matrix_and_kitti_errors_match_host(lt_name):
     np.testing.assert_allclose(trans.cpu().numpy(), ref[:, 1], atol=1e-12)
 
 
-@pytest.mark.parametrize('shape,mp', [(8, 0), (16, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 1), (16, 2), (16, 4), (16, 6), (32, 1), (32, 2)])
+@pytest.mark.parametrize('shape,mp', [(8, 0), (16, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 1), (16, 2), (16, 4), (32, 0)])
 def test_fps_multipick_variants_are_exact(p2, shape, mp, monkeypatch):
     """Every warps-per-cloud x samples-per-round variant of the bucketed kernels (fps_tmem.cu: minima in tensor memory,
     mp >= 1 samples per round; fps_bucket.cu: mp = 0, registers; DCLR_FPS_SHAPE / DCLR_FPS_MP are read per call) returns the indices of the serial algorithm (sampling_gpu.cu:113-208), under both tie

@@ -13,7 +13,7 @@ sys.path.insert(0, ROOT)
 from deepclr_b200 import _lib, synth  # noqa: E402
 
 pool = np.stack([synth.kitti_pair(1234 + i, 16384)[i % 2] for i in range(16)])
-variants = [(8, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 1), (16, 2), (16, 4), (16, 6), (32, 1), (32, 2)]
+variants = [(8, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 2), (16, 4)]
 if len(sys.argv) > 1:
     variants = [tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]]
 ref = None
