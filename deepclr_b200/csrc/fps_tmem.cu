@@ -132,6 +132,7 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     for (int r = 1; r < MP; ++r)
         if (lane >= r * (r - 1) / 2) { pr = r; pl = lane - r * (r - 1) / 2; }
     const bool pair_lane = lane < NPAIR;
+    if (!pair_lane) { pl = 0; pr = MP > 1 ? 1 : 0; }       // (idle lanes read a valid pair; their vote is masked)
     const int4 *cand = s_cand + warp * (2 * MP);  // this warp's copy of the first MP winners in order: {hi, lo, bound, -}, {x, y, z, -}
 
     // picks applied in the coming round: coordinates in registers (unused slots far away: they change nothing)
@@ -173,10 +174,10 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
             while (mask) {
                 // two buckets per iteration (the second repeats the first when only one is left: same values again)
                 int iu[2];
-                iu[0] = __ffs(mask) - 1;
-                mask &= mask - 1;
-                iu[1] = mask ? __ffs(mask) - 1 : iu[0];
-                mask &= mask - 1;
+                iu[0] = 31 - __clz(mask);               // highest first: one FLO (ffs = BREV + FLO, ~47 dependent cycles)
+                mask ^= 1u << iu[0];
+                iu[1] = mask ? 31 - __clz(mask) : iu[0];
+                mask &= ~(1u << iu[1]);
                 uint64_t X[2], Y[2], Z[2];
                 uint32_t id2[2], tlb[2], thb[2];
 #pragma unroll
