@@ -277,6 +277,15 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
             }
         }
         __syncwarp();
+        // the MP winners' coordinates, loaded before it is known how many are taken (off the vote's critical path)
+        uint32_t cx[MP], cy[MP], cz[MP];
+        const uint32_t cand_a = ptx::smem_u32(cand);
+#pragma unroll
+        for (int q = 0; q < MP; ++q) {
+            uint32_t pad;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(cx[q]), "=r"(cy[q]), "=r"(cz[q]), "=r"(pad)
+                         : "r"(cand_a + (2 * q + 1) * 16));
+        }
         int take = 1;
         if (MP > 1) {
             // lane p tests pair (pl, pr): the update's own arithmetic, point c_pr against sample c_pl
@@ -297,10 +306,9 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
         // next round's picks (uniform) ...
 #pragma unroll
         for (int q = 0; q < MP; ++q) {
-            const int4 cB = cand[2 * q + 1];
             const bool on = q < take;
-            px[q] = on ? __int_as_float(cB.x) : 1e18f; py[q] = on ? __int_as_float(cB.y) : 1e18f;
-            pz[q] = on ? __int_as_float(cB.z) : 1e18f;
+            px[q] = on ? __uint_as_float(cx[q]) : 1e18f; py[q] = on ? __uint_as_float(cy[q]) : 1e18f;
+            pz[q] = on ? __uint_as_float(cz[q]) : 1e18f;
         }
         MTRACEV(4, clock64() + (take & 0));
         MTRACEV(7, take);
