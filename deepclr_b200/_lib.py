@@ -48,7 +48,12 @@ _SIGNATURES = {
     'dclr_cloud_features': (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     'dclr_forward_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     'dclr_forward_pairs': (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    'dclr_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
+    'dclr_sa_msg_fused': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    'dclr_flow_embed_fused': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    'dclr_pose_head_fused': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     'dclr_model_last_launches': (c_int, [c_void_p]),
+    'dclr_model_generation': (c_int, [c_void_p]),
     'dclr_model_set_timing': (c_int, [c_void_p, c_int]),
     'dclr_model_stage_count': (c_int, []),
     'dclr_model_stage_name': (ctypes.c_char_p, [c_int]),

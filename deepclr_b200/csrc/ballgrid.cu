@@ -310,13 +310,17 @@ int ball_grid_launch(const float *new_xyz, const float *pts, int stride, int B, 
     float4 *sorted = (float4 *)w;
     int32_t *cellstart = (int32_t *)(w + (size_t)B * N * sizeof(float4));
     float *params = (float *)(w + (size_t)B * N * sizeof(float4) + (((size_t)B * (BG_CELLS + 1) * 4 + 255) / 256) * 256);
-    static bool attr_done = false;   // idempotent attribute set; benign if raced
-    if (!attr_done) {
+    // the opt-in is per DEVICE (a process may run models on several GPUs): one flag per device ordinal, idempotent set,
+    // benign if raced
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DCLR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
         DCLR_CUDA(cudaFuncSetAttribute(bq_grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        BG_CELLS * (int)sizeof(int)));
         DCLR_CUDA(cudaFuncSetAttribute(bq_grid_query_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         DCLR_CUDA(cudaFuncSetAttribute(bq_grid_query_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_done = true;
+        if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     if (phase != BG_PHASE_QUERY) {
         bq_grid_build_kernel<<<B, BG_BUILD_T, BG_CELLS * sizeof(int), st>>>(pts, stride, N, rq, sorted, cellstart, params);

@@ -297,9 +297,9 @@ int pm_to_cm_launch(const float *xyz, const float *feat, int ldf, int off, int G
     return DCLR_OK;
 }
 
-// channel-major in [G, 3+F, n] -> xyz [G,n,3], feat [G,n,F]
+// channel-major in [G, 3+F, n] -> xyz [G,n,3], feat [G,n,ldf] (F columns); xyz == nullptr: rows [xyz | features] in feat
 __global__ void cm_to_pm_kernel(const float *__restrict__ in, int n, int F, float *__restrict__ xyz,
-                                float *__restrict__ feat) {
+                                float *__restrict__ feat, int ldf) {
     __shared__ float tile[32][33];
     const int g = blockIdx.z;
     const int i0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -313,15 +313,16 @@ __global__ void cm_to_pm_kernel(const float *__restrict__ in, int n, int F, floa
         int i = i0 + r, c = c0 + threadIdx.x;
         if (i < n && c < C) {
             float v = tile[threadIdx.x][r];
-            if (c < 3) xyz[((size_t)g * n + i) * 3 + c] = v;
-            else feat[((size_t)g * n + i) * F + c - 3] = v;
+            if (!xyz) feat[((size_t)g * n + i) * ldf + c] = v;
+            else if (c < 3) xyz[((size_t)g * n + i) * 3 + c] = v;
+            else feat[((size_t)g * n + i) * ldf + c - 3] = v;
         }
     }
 }
 
-int cm_to_pm_launch(const float *in, int G, int n, int F, float *xyz, float *feat, cudaStream_t st) {
+int cm_to_pm_launch(const float *in, int G, int n, int F, float *xyz, float *feat, int ldf, cudaStream_t st) {
     dim3 grid(div_up(n, 32), div_up(3 + F, 32), G);
-    cm_to_pm_kernel<<<grid, dim3(32, 8), 0, st>>>(in, n, F, xyz, feat);
+    cm_to_pm_kernel<<<grid, dim3(32, 8), 0, st>>>(in, n, F, xyz, feat, ldf);
     DCLR_LAUNCH_CHECK("cm_to_pm_kernel");
     return DCLR_OK;
 }

@@ -70,6 +70,6 @@ int rowmax_launch(const float *H, int ldh, int B, int n, int C, float *out, cuda
 int pose_activation_launch(float *y, int B, int dim, int label_type, cudaStream_t st);
 int pm_to_cm_launch(const float *xyz, const float *feat, int ldf, int off, int G, int n, int F, float *out,
                     cudaStream_t st);
-int cm_to_pm_launch(const float *in, int G, int n, int F, float *xyz, float *feat, cudaStream_t st);
+int cm_to_pm_launch(const float *in, int G, int n, int F, float *xyz, float *feat, int ldf, cudaStream_t st);
 
 }  // namespace dclr

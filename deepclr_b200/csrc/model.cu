@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "mlp_tc.cuh"
+#include <nvtx3/nvToolsExt.h>
 #include <new>
 #include <vector>
 
@@ -19,6 +20,7 @@ struct dclr_model {
     // workspace
     void *ws = nullptr;
     size_t ws_bytes = 0;
+    int ws_generation = 0;           // bumped whenever the workspace moves: graphs captured before are stale
     int last_launches = 0;
     // carved pointers (valid after ensure_ws)
     int32_t *fps_idx, *bq_idx[2], *bq_cnt[2], *knn_col;
@@ -33,7 +35,7 @@ struct dclr_model {
     cudaEvent_t *ev = nullptr;
     // side stream: work that reads only the input cloud runs next to FPS (which leaves 20 of the 148 SMs idle)
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fps = nullptr, ev_knn = nullptr;
     int ev_calls = 0;                // calls recorded since the last collect (may exceed the ring)
     int ev_cur = 0;                  // slot of the call being recorded
     uint32_t ev_mask[64] = {0};      // stages recorded per ring slot
@@ -99,6 +101,7 @@ static int ensure_ws(dclr_model *m, int G, int N, int B) {
         m->ws_bytes = 0;
         DCLR_CUDA(cudaMalloc(&m->ws, need));
         m->ws_bytes = need;
+        ++m->ws_generation;
     }
     carve(m, (char *)m->ws, G, N, B);
     return DCLR_OK;
@@ -124,10 +127,18 @@ static void timing_mark(dclr_model *m, int s, int which, cudaStream_t st) {
     m->ev_mask[m->ev_cur] |= 1u << s;
     cudaEventRecord(m->ev[(size_t)m->ev_cur * EV_PER_CALL + 2 * s + which], st);
 }
+// one stage of a forward: CUDA-event pair when timing is on (the reference times with an event pair around predict,
+// scripts/timing.py:32-47) + an NVTX range named after the stage for timeline tools (free when no tool is attached)
 struct StageScope {
     dclr_model *m; int s; cudaStream_t st;
-    StageScope(dclr_model *m_, int s_, cudaStream_t st_) : m(m_), s(s_), st(st_) { timing_mark(m, s, 0, st); }
-    ~StageScope() { timing_mark(m, s, 1, st); }
+    StageScope(dclr_model *m_, int s_, cudaStream_t st_) : m(m_), s(s_), st(st_) {
+        nvtxRangePushA(kStageNames[s]);
+        timing_mark(m, s, 0, st);
+    }
+    ~StageScope() {
+        timing_mark(m, s, 1, st);
+        nvtxRangePop();
+    }
 };
 
 #define DCLR_TRY(expr)            \
@@ -138,7 +149,11 @@ struct StageScope {
     } while (0)
 
 // FPS -> ball query (both radii, one pass) -> grouped MLP + max-pool.  pointnet2_modules.py:19-55
-static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cudaStream_t st) {
+// knn_pairs > 0: the kNN of the merge stage (it reads only the FPS samples) is forked onto the side stream right after
+// FPS, next to ball query + grouped MLP; the caller joins with ev_knn before the flow embedding.
+// centres != nullptr: the caller supplies the sampled centres [G,npoint,3] (dclr_sa_msg_fused): no FPS.
+static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cudaStream_t st, int knn_pairs = 0,
+                               const float *centres = nullptr) {
     const dclr_arch &a = m->arch;
     // The ball-query grid build (counting sort of the cloud into cells, ~40 us for 128 KITTI clouds) depends on the
     // input only, and the sampling kernel (one CTA per cloud, latency-bound) leaves SMs and issue slots idle for
@@ -149,8 +164,13 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
         DCLR_CUDA(cudaStreamCreateWithPriority(&m->side, cudaStreamNonBlocking, lo));
         DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
         DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
+        DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_fps, cudaEventDisableTiming));
+        DCLR_CUDA(cudaEventCreateWithFlags(&m->ev_knn, cudaEventDisableTiming));
     }
-    {
+    if (centres) {
+        DCLR_CUDA(cudaMemcpyAsync(m->new_xyz, centres, (size_t)G * a.npoint * 3 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        DCLR_CUDA(cudaEventRecord(m->ev_fork, st));
+    } else {
         StageScope sc(m, ST_FPS, st);
         int used = 0;
         DCLR_TRY(fps_bucket_launch(x, a.input_dim, G, N, a.npoint, m->tie_rule, m->fps_idx, m->new_xyz, m->fps_ws, st, &used,
@@ -168,6 +188,18 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
                                   m->bq_cnt, /*pad=*/0, m->bq_ws, m->side, &grid_built, BG_PHASE_BUILD));
         if (!grid_built) --m->last_launches;               // shape not handled by the grid: nothing was launched
         DCLR_CUDA(cudaEventRecord(m->ev_join, m->side));
+    }
+    if (knn_pairs > 0) {
+        // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
+        const size_t BM = (size_t)knn_pairs * a.npoint;
+        DCLR_CUDA(cudaEventRecord(m->ev_fps, st));
+        DCLR_CUDA(cudaStreamWaitEvent(m->side, m->ev_fps, 0));
+        {
+            StageScope sc(m, ST_KNN, m->side);
+            DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, knn_pairs, a.npoint, a.npoint, a.knn_k, nullptr, nullptr,
+                                m->knn_col, m->knn_nbr4, m->side));
+        }
+        DCLR_CUDA(cudaEventRecord(m->ev_knn, m->side));
     }
     {
         DCLR_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
@@ -194,41 +226,62 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
     return DCLR_OK;
 }
 
-// kNN grouping + motion embedding + output head on point-major SA features.  deepclr.py:157-231, 284-294
-static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_out, cudaStream_t st) {
+// kNN grouping + motion embedding on point-major SA features (deepclr.py:157-231): leaves the motion features in the
+// workspace (16-bit image for the tensor-core head, fp32 `motion` when tapped / in fp32 mode)
+static int run_flow(dclr_model *m, int B, bool tap_motion, cudaStream_t st, bool knn_forked) {
     const dclr_arch &a = m->arch;
     const int M = a.npoint, k = a.knn_k, F = m->F;
     const size_t BM = (size_t)B * M, R = BM * k;
     const int ldm = (int)align_up(3 + a.merge_mlp[2], 4);
-    // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
-    {
+    if (knn_forked) {
+        DCLR_CUDA(cudaStreamWaitEvent(st, m->ev_knn, 0));
+    } else {
+        // candidates x = source samples (clouds B..2B-1), queries y = template samples (deepclr.py:164-166)
         StageScope sc(m, ST_KNN, st);
         DCLR_TRY(knn_launch(m->new_xyz + BM * 3, m->new_xyz, B, M, M, k, nullptr, nullptr, m->knn_col, m->knn_nbr4, st));
     }
+    StageScope sc(m, ST_FLOW, st);
     if (m->numerics != 0) {
-        {
-            StageScope sc(m, ST_FLOW, st);
-            // fp32 motion features only when the caller taps them; the head reads the 16-bit image
-            DCLR_TRY(tc_flow(m->tc, m->sa_feat16, m->knn_nbr4, B, M, m->motion16,
-                             motion_out ? m->motion : nullptr, st));
-        }
+        // fp32 motion features only when the caller taps them; the head reads the 16-bit image
+        DCLR_TRY(tc_flow(m->tc, m->sa_feat16, m->knn_nbr4, B, M, m->motion16, tap_motion ? m->motion : nullptr, st));
+        return DCLR_OK;
+    }
+    const int ld0 = (int)align_up(m->nmerge_in, 4);
+    DCLR_TRY(flow_rows_launch(m->new_xyz, m->sa_feat, m->knn_col, B, M, k, F, a.merge_radius, m->rows, ld0, m->mask, st));
+    DCLR_TRY(linear_f32_launch(m->rows, ld0, m->merge[0].W, m->merge[0].b, m->h1, a.merge_mlp[0], (int)R, a.merge_mlp[0],
+                               m->nmerge_in, 1, st));
+    DCLR_TRY(linear_f32_launch(m->h1, a.merge_mlp[0], m->merge[1].W, m->merge[1].b, m->h2, a.merge_mlp[1], (int)R,
+                               a.merge_mlp[1], a.merge_mlp[0], 1, st));
+    DCLR_TRY(linear_f32_launch(m->h2, a.merge_mlp[1], m->merge[2].W, m->merge[2].b, m->h3, a.merge_mlp[2], (int)R,
+                               a.merge_mlp[2], a.merge_mlp[1], 1, st));
+    DCLR_TRY(masked_groupmax_launch(m->h3, a.merge_mlp[2], m->mask, m->new_xyz, BM, k, a.merge_mlp[2], m->motion, ldm, st));
+    return DCLR_OK;
+}
+
+// reference layout [B, 3 + merge_mlp[2], npoint] of the motion features left by run_flow
+static int motion_to_reference_layout(dclr_model *m, int B, float *motion_out, cudaStream_t st) {
+    const dclr_arch &a = m->arch;
+    StageScope sc(m, ST_LAYOUT, st);
+    if (m->numerics != 0)    // tensor-core path keeps features only; coordinates are the template samples
+        DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->motion, a.merge_mlp[2], 0, B, a.npoint, a.merge_mlp[2], motion_out, st));
+    else
+        DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, (int)align_up(3 + a.merge_mlp[2], 4), 0, B, a.npoint, a.merge_mlp[2],
+                                 motion_out, st));
+    return DCLR_OK;
+}
+
+// output head on the motion features in the workspace (deepclr.py:284-294): 5 x (1x1 conv + ReLU) -> max over the points
+// -> 2 x (Linear + ReLU) -> Linear -> activation
+static int run_head(dclr_model *m, int B, float *y_out, cudaStream_t st) {
+    const dclr_arch &a = m->arch;
+    const int M = a.npoint;
+    const size_t BM = (size_t)B * M;
+    const int ldm = (int)align_up(3 + a.merge_mlp[2], 4);
+    if (m->numerics != 0) {
         StageScope sc(m, ST_HEAD, st);
         DCLR_TRY(tc_head(m->tc, m->new_xyz, m->motion16, B, M, m->pooled, st));
     } else {
-        timing_mark(m, ST_FLOW, 0, st);
-        const int ld0 = (int)align_up(m->nmerge_in, 4);
-        DCLR_TRY(flow_rows_launch(m->new_xyz, m->sa_feat, m->knn_col, B, M, k, F, a.merge_radius, m->rows, ld0,
-                                  m->mask, st));
-        DCLR_TRY(linear_f32_launch(m->rows, ld0, m->merge[0].W, m->merge[0].b, m->h1, a.merge_mlp[0], (int)R,
-                                   a.merge_mlp[0], m->nmerge_in, 1, st));
-        DCLR_TRY(linear_f32_launch(m->h1, a.merge_mlp[0], m->merge[1].W, m->merge[1].b, m->h2, a.merge_mlp[1], (int)R,
-                                   a.merge_mlp[1], a.merge_mlp[0], 1, st));
-        DCLR_TRY(linear_f32_launch(m->h2, a.merge_mlp[1], m->merge[2].W, m->merge[2].b, m->h3, a.merge_mlp[2], (int)R,
-                                   a.merge_mlp[2], a.merge_mlp[1], 1, st));
-        DCLR_TRY(masked_groupmax_launch(m->h3, a.merge_mlp[2], m->mask, m->new_xyz, BM, k, a.merge_mlp[2], m->motion,
-                                        ldm, st));
-        timing_mark(m, ST_FLOW, 1, st);
-        timing_mark(m, ST_HEAD, 0, st);
+        StageScope sc(m, ST_HEAD, st);
         const float *in = m->motion;
         int ldin = ldm, kin = m->head_in;
         float *bufs[2] = {m->actA, m->actB};
@@ -239,9 +292,8 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
             in = out; ldin = a.out_mlp[l]; kin = a.out_mlp[l];
         }
         DCLR_TRY(rowmax_launch(in, ldin, B, M, a.out_mlp[4], m->pooled, st));
-        timing_mark(m, ST_HEAD, 1, st);
     }
-    timing_mark(m, ST_TAIL, 0, st);
+    StageScope sc(m, ST_TAIL, st);
     // fully connected tail: helper.py:97-123 (ReLU after both), final nn.Linear, activation deepclr.py:275-282
     if (a.out_linear[0] % 4 == 0 && a.out_linear[1] % 4 == 0 && a.out_linear[2] % 4 == 0) {
         DCLR_TRY(linear_skinny_launch(m->pooled, a.out_mlp[4], m->lin[0].W, m->lin[0].b, m->t1, a.out_linear[1], B,
@@ -259,15 +311,16 @@ static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_ou
                                    a.out_linear[2], 0, st));
         DCLR_TRY(pose_activation_launch(y_out, B, m->label_dim, a.label_type, st));
     }
-    timing_mark(m, ST_TAIL, 1, st);
-    if (motion_out) {
-        StageScope sc(m, ST_LAYOUT, st);
-        if (m->numerics != 0)    // tensor-core path keeps features only; coordinates are the template samples
-            DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->motion, a.merge_mlp[2], 0, B, M, a.merge_mlp[2], motion_out, st));
-        else
-            DCLR_TRY(pm_to_cm_launch(nullptr, m->motion, ldm, 0, B, M, a.merge_mlp[2], motion_out, st));
-    }
     return DCLR_OK;
+}
+
+static int run_merge_output(dclr_model *m, int B, float *y_out, float *motion_out, cudaStream_t st,
+                            bool knn_forked = false) {
+    int rc = run_flow(m, B, motion_out != nullptr, st, knn_forked);
+    if (rc != DCLR_OK) return rc;
+    rc = run_head(m, B, y_out, st);
+    if (rc != DCLR_OK) return rc;
+    return motion_out ? motion_to_reference_layout(m, B, motion_out, st) : DCLR_OK;
 }
 
 }  // namespace dclr
@@ -283,6 +336,10 @@ extern "C" int dclr_model_create(const dclr_arch *arch, const float *weights, si
     DCLR_CHECK_ARG(a.npoint >= 1 && a.knn_k >= 1 && a.knn_k <= 128, "need npoint >= 1 and 1 <= k <= 128");
     DCLR_CHECK_ARG(a.label_type >= 0 && a.label_type <= 2, "label_type must be 0..2");
     DCLR_CHECK_ARG(a.out_linear[0] == a.out_mlp[4], "out_linear[0] must equal out_mlp[4]");
+    for (int s = 0; s < a.num_scales; ++s)       // the grouped-MLP kernel is built for the reference widths only (sa_mlp.cu)
+        if (a.sa_mlp[s][0] != 16 || a.sa_mlp[s][1] != 16 || a.sa_mlp[s][2] != 32)
+            return fail(DCLR_E_UNSUPPORTED, "dclr_model_create: set-abstraction MLP of scale %d is [%d,%d,%d]; only "
+                        "[16,16,32] is built", s, a.sa_mlp[s][0], a.sa_mlp[s][1], a.sa_mlp[s][2]);
     dclr_model *m = new (std::nothrow) dclr_model();
     DCLR_CHECK_ARG(m, "out of host memory");
     m->arch = a;
@@ -348,6 +405,8 @@ extern "C" void dclr_model_destroy(dclr_model *m) {
     if (m->d_w) cudaFree(m->d_w);
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);
+    if (m->ev_fps) cudaEventDestroy(m->ev_fps);
+    if (m->ev_knn) cudaEventDestroy(m->ev_knn);
     if (m->side) cudaStreamDestroy(m->side);
     delete m;
 }
@@ -407,7 +466,7 @@ extern "C" int dclr_forward_features(dclr_model *m, const float *feat, int B, fl
     if (rc != DCLR_OK) return rc;
     {
         StageScope sc(m, ST_LAYOUT, st);
-        DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, st));
+        DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, m->F, st));
         if (m->numerics != 0)
             DCLR_TRY(tc_convert(m->tc, m->sa_feat, m->sa_feat16, (size_t)2 * B * m->arch.npoint * m->F, st));
     }
@@ -424,16 +483,86 @@ extern "C" int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, f
     timing_begin_call(m);
     int rc = ensure_ws(m, 2 * B, N, B);
     if (rc != DCLR_OK) return rc;
-    rc = run_set_abstraction(m, x, 2 * B, N, st);
+    rc = run_set_abstraction(m, x, 2 * B, N, st, /*knn_pairs=*/B);
     if (rc != DCLR_OK) return rc;
     if (feat_out) {
         StageScope sc(m, ST_LAYOUT, st);
         DCLR_TRY(pm_to_cm_launch(m->new_xyz, m->sa_feat, m->F, 0, 2 * B, m->arch.npoint, m->F, feat_out, st));
     }
-    return run_merge_output(m, B, y_out, motion_out, st);
+    return run_merge_output(m, B, y_out, motion_out, st, /*knn_forked=*/true);
+}
+
+// ---- stage-level entries: the three fused stacks one by one, for op-level parity and sweeps
+extern "C" size_t dclr_workspace_bytes(const dclr_model *m, int num_clouds, int N) {
+    if (!m || num_clouds < 1 || N < 1) return 0;
+    dclr_model probe = *m;                       // carve() only writes the carved pointers of its argument
+    probe.tc = nullptr;
+    const size_t need = carve(&probe, nullptr, num_clouds, N, (num_clouds + 1) / 2);
+    probe.ev = nullptr; probe.ws = nullptr; probe.d_w = nullptr; probe.side = nullptr;
+    return need;
+}
+
+extern "C" int dclr_sa_msg_fused(dclr_model *m, const float *x, const float *new_xyz, int num_clouds, int N,
+                                 float *feat_out, void *stream) {
+    DCLR_CHECK_ARG(m && x && new_xyz && feat_out, "dclr_sa_msg_fused: null pointer");
+    DCLR_CHECK_ARG(num_clouds >= 1 && N >= 1, "dclr_sa_msg_fused: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    m->last_launches = 0;
+    timing_begin_call(m);
+    int rc = ensure_ws(m, num_clouds, N, (num_clouds + 1) / 2);
+    if (rc != DCLR_OK) return rc;
+    rc = run_set_abstraction(m, x, num_clouds, N, st, 0, new_xyz);
+    if (rc != DCLR_OK) return rc;
+    StageScope sc(m, ST_LAYOUT, st);             // features only, [G, F, npoint] as PointnetSAModuleMSG returns them
+    DCLR_TRY(pm_to_cm_launch(nullptr, m->sa_feat, m->F, 0, num_clouds, m->arch.npoint, m->F - 3, feat_out, st));
+    return DCLR_OK;
+}
+
+extern "C" int dclr_flow_embed_fused(dclr_model *m, const float *feat, int B, float *motion_out, void *stream) {
+    DCLR_CHECK_ARG(m && feat && motion_out, "dclr_flow_embed_fused: null pointer");
+    DCLR_CHECK_ARG(B >= 1, "dclr_flow_embed_fused: bad batch");
+    DCLR_CHECK_ARG(m->arch.knn_k <= m->arch.npoint, "knn k=%d exceeds npoint=%d", m->arch.knn_k, m->arch.npoint);
+    cudaStream_t st = (cudaStream_t)stream;
+    m->last_launches = 0;
+    timing_begin_call(m);
+    int rc = ensure_ws(m, 2 * B, 1, B);
+    if (rc != DCLR_OK) return rc;
+    {
+        StageScope sc(m, ST_LAYOUT, st);
+        DCLR_TRY(cm_to_pm_launch(feat, 2 * B, m->arch.npoint, m->F, m->new_xyz, m->sa_feat, m->F, st));
+        if (m->numerics != 0)
+            DCLR_TRY(tc_convert(m->tc, m->sa_feat, m->sa_feat16, (size_t)2 * B * m->arch.npoint * m->F, st));
+    }
+    rc = run_flow(m, B, true, st, false);
+    if (rc != DCLR_OK) return rc;
+    return motion_to_reference_layout(m, B, motion_out, st);
+}
+
+extern "C" int dclr_pose_head_fused(dclr_model *m, const float *motion, int B, float *y_out, void *stream) {
+    DCLR_CHECK_ARG(m && motion && y_out, "dclr_pose_head_fused: null pointer");
+    DCLR_CHECK_ARG(B >= 1, "dclr_pose_head_fused: bad batch");
+    cudaStream_t st = (cudaStream_t)stream;
+    const dclr_arch &a = m->arch;
+    m->last_launches = 0;
+    timing_begin_call(m);
+    int rc = ensure_ws(m, 2 * B, 1, B);
+    if (rc != DCLR_OK) return rc;
+    {
+        StageScope sc(m, ST_LAYOUT, st);
+        const size_t BM = (size_t)B * a.npoint;
+        if (m->numerics != 0) {      // coordinates -> new_xyz, features -> fp32 rows -> the head's 16-bit operand image
+            DCLR_TRY(cm_to_pm_launch(motion, B, a.npoint, a.merge_mlp[2], m->new_xyz, m->motion, a.merge_mlp[2], st));
+            DCLR_TRY(tc_convert(m->tc, m->motion, m->motion16, BM * a.merge_mlp[2], st));
+        } else {                     // rows [xyz | features] with the SIMT head's leading dimension
+            DCLR_TRY(cm_to_pm_launch(motion, B, a.npoint, a.merge_mlp[2], nullptr, m->motion,
+                                     (int)align_up(3 + a.merge_mlp[2], 4), st));
+        }
+    }
+    return run_head(m, B, y_out, st);
 }
 
 extern "C" int dclr_model_last_launches(const dclr_model *m) { return m ? m->last_launches : 0; }
+extern "C" int dclr_model_generation(const dclr_model *m) { return m ? m->ws_generation : -1; }
 
 extern "C" int dclr_model_set_timing(dclr_model *m, int on) {
     DCLR_CHECK_ARG(m, "null model");

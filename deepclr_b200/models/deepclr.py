@@ -376,6 +376,13 @@ class DeepCLR(BaseModel):
         return self._cloud_layers(x.transpose(1, 2))
 
     # ---- fused route
+    def graph_token(self, device: torch.device):
+        """Identity of everything a CUDA graph captured from this model's fused forward points at: the native handle
+        (rebuilt when parameters, numerics or the tie rule change) and its workspace generation (bumped when a larger
+        shape re-allocates it).  GraphedForward / HostPipeline / ModelInferenceHelper re-capture when it changes."""
+        native = self._get_native(device)
+        return (id(native), native.generation())
+
     def _fused_supported(self) -> bool:
         sa, me, out = self._cloud_layers[-1], self._merge_layers[0], self._merge_layers[1]
         if len(self._cloud_layers) != 1 or not isinstance(sa, SetAbstraction) or sa._sa1 is not None:
@@ -384,10 +391,27 @@ class DeepCLR(BaseModel):
             return False
         emb = me._embedding
         spec = sa._spec
-        return (emb._k > 0 and emb._append_features and len(spec['radii'][0]) in (1, 2)
-                and all(len(mm) == 3 for mm in spec['mlps'][0])
+        if not (emb._append_features and len(spec['radii'][0]) in (1, 2)
                 and len(emb._conv._sequential) == 3 and len(out.conv._sequential) == 5
-                and len(out.linear._sequential) == 2)
+                and len(out.linear._sequential) == 2):
+            return False
+        # every constraint of the native kernels (csrc/sa_mlp.cu: sa_mlp_launch, csrc/model.cu: dclr_model_create,
+        # csrc/mlp_tc.cu: tc_create); any other legal reference config runs the composed route
+        if spec['input_dim'] not in (3, 4) or any(list(mm) != [16, 16, 32] for mm in spec['mlps'][0]):
+            return False
+        if not 1 <= emb._k <= min(128, spec['npoint'][0]):
+            return False
+        if self.numerics != 'fp32':
+            F = 32 * len(spec['mlps'][0])
+            merge = [b.output_dim() for b in emb._conv._sequential]
+            head = [b.output_dim() for b in out.conv._sequential]
+            if merge[:2] != [128, 128] or merge[2] not in (128, 256):
+                return False
+            if emb._conv._sequential[0]._sequential[0].in_channels != 2 * F + 3:
+                return False
+            if any(h % 128 for h in head) or any(h > 512 for h in head[:-1]):
+                return False
+        return True
 
     def _fused_ok(self, x: torch.Tensor, m: Optional[torch.Tensor]) -> bool:
         if not x.is_cuda:

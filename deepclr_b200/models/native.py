@@ -107,6 +107,50 @@ class NativeModel:
                                                      _lib.ptr(motion), _lib.stream_ptr()), 'dclr_forward_pairs')
         return y, feat, motion
 
+    # ---- stage-level entries (include/deepclr_b200.h)
+    def workspace_bytes(self, num_clouds: int, n_points: int) -> int:
+        return int(_lib.lib().dclr_workspace_bytes(self._handle, num_clouds, n_points))
+
+    def sa_msg(self, x: torch.Tensor, new_xyz: torch.Tensor) -> torch.Tensor:
+        """x [G,N,C], centres new_xyz [G,npoint,3] -> features [G,F,npoint] (PointnetSAModuleMSG after its sampling)."""
+        x, new_xyz = self._prep(x), self._prep(new_xyz)
+        G, N, _ = x.shape
+        if tuple(new_xyz.shape) != (G, self.npoint, 3):
+            raise RuntimeError(f'new_xyz must be [{G},{self.npoint},3], got {tuple(new_xyz.shape)}')
+        out = torch.empty((G, self.feat_dim - 3, self.npoint), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dclr_sa_msg_fused(self._handle, _lib.ptr(x), _lib.ptr(new_xyz), G, N, _lib.ptr(out),
+                                                    _lib.stream_ptr()), 'dclr_sa_msg_fused')
+        return out
+
+    def flow_embed(self, feat: torch.Tensor) -> torch.Tensor:
+        """feat [2B,3+F,npoint] templates first -> motion embedding [B,3+C,npoint] (MotionEmbedding.forward)."""
+        feat = self._prep(feat)
+        if feat.shape[0] % 2 or feat.shape[1] != self.feat_dim or feat.shape[2] != self.npoint:
+            raise RuntimeError(f'features must be [2B,{self.feat_dim},{self.npoint}], got {tuple(feat.shape)}')
+        B = feat.shape[0] // 2
+        out = torch.empty((B, self.motion_dim, self.npoint), dtype=torch.float32, device=feat.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dclr_flow_embed_fused(self._handle, _lib.ptr(feat), B, _lib.ptr(out),
+                                                        _lib.stream_ptr()), 'dclr_flow_embed_fused')
+        return out
+
+    def pose_head(self, motion: torch.Tensor) -> torch.Tensor:
+        """motion [B,3+C,npoint] -> pose labels [B,label_dim] (OutputSimple.forward)."""
+        motion = self._prep(motion)
+        if motion.shape[1] != self.motion_dim or motion.shape[2] != self.npoint:
+            raise RuntimeError(f'motion must be [B,{self.motion_dim},{self.npoint}], got {tuple(motion.shape)}')
+        B = motion.shape[0]
+        y = torch.empty((B, self.label_dim), dtype=torch.float32, device=motion.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dclr_pose_head_fused(self._handle, _lib.ptr(motion), B, _lib.ptr(y),
+                                                       _lib.stream_ptr()), 'dclr_pose_head_fused')
+        return y
+
+    def generation(self) -> int:
+        """Workspace generation of the handle (include/deepclr_b200.h: dclr_model_generation)."""
+        return int(_lib.lib().dclr_model_generation(self._handle))
+
     def last_launches(self) -> int:
         return int(_lib.lib().dclr_model_last_launches(self._handle))
 

@@ -11,6 +11,13 @@ from typing import Iterable, Iterator, List, Optional
 import torch
 
 
+def _graph_token(model, device):
+    """What a graph captured from `model`'s forward depends on besides its input buffer (DeepCLR.graph_token: native
+    handle identity + workspace generation); models without a native handle have none."""
+    fn = getattr(model, 'graph_token', None)
+    return fn(device) if fn is not None else None
+
+
 class HostPipeline:
     """`for y in HostPipeline(model).run(batches): ...` -- `batches` yields pinned (or pageable) CPU tensors
     [2B, N, C] (templates first, deepclr/data/build.py:82); yields CPU tensors [B, label_dim] in order.
@@ -37,24 +44,32 @@ class HostPipeline:
         self._done = [torch.cuda.Event() for _ in range(self.depth + 1)]
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._main_stream = None                  # the stream run() computes on (set there)
 
     def _stage(self, slot: int, host: torch.Tensor) -> None:
         buf = self._in[slot]
-        if buf is None or buf.shape != host.shape:
-            buf = self._in[slot] = torch.empty(host.shape, dtype=torch.float32, device=self.device)
         with torch.cuda.stream(self._copy):
             if self._used[slot]:
                 self._copy.wait_event(self._freed[slot])       # the forward that read this buffer has finished
+            if buf is None or buf.shape != host.shape:
+                # (re)allocated ON the copy stream, after the wait above: the caching allocator then never hands out a
+                # block that kernels queued on the main stream still use, and the old buffer is released only once the
+                # forward that read it is done; the main stream is recorded as a user of the new block
+                buf = self._in[slot] = torch.empty(host.shape, dtype=torch.float32, device=self.device)
+                buf.record_stream(self._main())
             buf.copy_(host, non_blocking=True)
             self._loaded[slot].record(self._copy)
         self._used[slot] = True
         self.h2d_bytes += host.numel() * host.element_size()
 
+    def _main(self):
+        return torch.cuda.default_stream(self.device) if self._main_stream is None else self._main_stream
+
     def _forward(self, slot: int) -> torch.Tensor:
         x = self._in[slot]
         if not self._use_graph:
             return self.model(x)[0]
-        key = (slot, x.data_ptr(), tuple(x.shape))
+        key = (slot, x.data_ptr(), tuple(x.shape), _graph_token(self.model, self.device))
         hit = self._graphs.get(slot)
         if hit is None or hit[0] != key:
             # first batch of this shape in this slot: run it directly (this also sizes the native workspace), then
@@ -64,6 +79,8 @@ class HostPipeline:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, capture_error_mode='thread_local'):   # other threads (NCCL watchdog) may call CUDA
                 y_static = self.model(x)[0]
+            # the capture itself may have grown the workspace of ANOTHER slot's shape: key on the token after it
+            key = key[:3] + (_graph_token(self.model, self.device),)
             self._graphs[slot] = (key, g, y_static)
             return y
         hit[1].replay()
@@ -73,7 +90,7 @@ class HostPipeline:
         it = iter(batches)
         nxt = next(it, None)
         i = 0
-        main = torch.cuda.current_stream(self.device)
+        main = self._main_stream = torch.cuda.current_stream(self.device)
         if nxt is not None:
             self._stage(0, nxt)
         while nxt is not None:
@@ -137,14 +154,15 @@ class RawScanPipeline(HostPipeline):
         if total != sum(lengths):
             raise ValueError('stage rows != sum(lengths)')
         buf = self._in[slot]
-        if buf is None or buf[0].shape[0] < total or buf[0].shape[1] != C or buf[1].shape[0] < len(lengths) + 1:
-            cap = int(total * 1.25) + 1
-            buf = self._in[slot] = (torch.empty((cap, C), dtype=torch.float32, device=self.device),
-                                    torch.empty(len(lengths) + 1, dtype=torch.int32, device=self.device))
-            self._used[slot] = False
         with torch.cuda.stream(self._copy):
             if self._used[slot]:
                 self._copy.wait_event(self._freed[slot])
+            if buf is None or buf[0].shape[0] < total or buf[0].shape[1] != C or buf[1].shape[0] < len(lengths) + 1:
+                cap = int(total * 1.25) + 1               # allocated on the copy stream, after the wait (see HostPipeline)
+                buf = self._in[slot] = (torch.empty((cap, C), dtype=torch.float32, device=self.device),
+                                        torch.empty(len(lengths) + 1, dtype=torch.int32, device=self.device))
+                for t in buf:
+                    t.record_stream(self._main())
             # a fresh pinned block per batch: torch's caching host allocator hands it out again only after this copy
             off = torch.empty(len(lengths) + 1, dtype=torch.int32, pin_memory=True)
             off[0] = 0
@@ -189,19 +207,31 @@ class GraphedForward:
         else:
             self.static_x = torch.empty(tuple(example.shape), dtype=torch.float32, device=dev)
             self.static_x.copy_(example)
+        self._dev, self._warmup = dev, max(1, warmup)
+        self.captures = 0
+        self._capture()
+
+    def _capture(self) -> None:
+        dev, model = self._dev, self.model
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side), torch.no_grad():
-            for _ in range(max(1, warmup)):      # sizes the native workspace, creates the side stream: no cudaMalloc later
+            for _ in range(self._warmup):        # sizes the native workspace, creates the side stream: no cudaMalloc later
                 model(self.static_x)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph, capture_error_mode='thread_local'), torch.no_grad():
             self.static_y = model(self.static_x)[0]
+        self._token = _graph_token(model, dev)
+        self.captures += 1
 
     def replay(self) -> torch.Tensor:
-        """Forward over the current content of the static input buffer."""
+        """Forward over the current content of the static input buffer.  The graph holds pointers into the native
+        handle's workspace and weights: when either was replaced since the capture (another shape grew the workspace,
+        `load_state_dict` / a numerics change rebuilt the handle) the forward is captured again first."""
+        if _graph_token(self.model, self._dev) != self._token:
+            self._capture()
         self.graph.replay()
         return self.static_y
 
@@ -209,5 +239,4 @@ class GraphedForward:
         if tuple(x.shape) != tuple(self.static_x.shape):
             raise ValueError(f'graph captured for {tuple(self.static_x.shape)}, got {tuple(x.shape)}')
         self.static_x.copy_(x, non_blocking=True)
-        self.graph.replay()
-        return self.static_y
+        return self.replay()

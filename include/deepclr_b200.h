@@ -148,8 +148,38 @@ int dclr_forward_features(dclr_model *m, const float *feat, int B, float *y_out,
 int dclr_forward_pairs(dclr_model *m, const float *x, int B, int N, float *y_out, float *feat_out,
                        float *motion_out, void *stream);
 
+/*
+ * Stage-level entries: the three fused stacks of the path one by one (op-level parity and sweeps).
+ *
+ * dclr_sa_msg_fused: ball query of both radii + grouping + shared MLP + max-pool around GIVEN centres = what
+ *   PointnetSAModuleMSG.forward does after its sampling (pointnet2_modules.py:37-55: QueryAndGroup -> SharedMLP ->
+ *   max_pool2d per scale, concatenated).  x [num_clouds, N, input_dim], new_xyz [num_clouds, npoint, 3] ->
+ *   feat_out [num_clouds, F, npoint] (features only, the reference's new_features layout).
+ * dclr_flow_embed_fused: kNN grouping + flow-embedding MLP + radius mask + max over the neighbours =
+ *   MotionEmbedding.forward (deepclr/models/deepclr.py:201-246).  feat [2B, 3+F, npoint] templates first ->
+ *   motion_out [B, 3+merge_mlp[2], npoint].
+ * dclr_pose_head_fused: OutputSimple.forward (deepclr.py:284-294).  motion [B, 3+merge_mlp[2], npoint] -> y_out
+ *   [B, label_dim].
+ * dclr_workspace_bytes: device bytes a call with num_clouds clouds of N points makes the handle hold (0 on bad arguments);
+ *   the workspace is allocated lazily and only ever grows (see dclr_model_generation).
+ *
+ * Threading contract of a handle: calls on ONE dclr_model must not overlap (one workspace, one side stream; they are
+ * ordered by the caller's stream); different handles are independent and may be driven from different threads and
+ * streams concurrently.  The library keeps no process-wide mutable state besides a per-device scratch pool behind a lock
+ * (op-level entries) and per-device one-time kernel attributes.
+ */
+size_t dclr_workspace_bytes(const dclr_model *m, int num_clouds, int N);
+int dclr_sa_msg_fused(dclr_model *m, const float *x, const float *new_xyz, int num_clouds, int N, float *feat_out,
+                      void *stream);
+int dclr_flow_embed_fused(dclr_model *m, const float *feat, int B, float *motion_out, void *stream);
+int dclr_pose_head_fused(dclr_model *m, const float *motion, int B, float *y_out, void *stream);
+
 /* Number of kernels the last dclr_forward_* / dclr_cloud_features call on this model enqueued. */
 int dclr_model_last_launches(const dclr_model *m);
+/* Workspace generation: grows by one each time a call had to re-allocate the handle's workspace (a larger shape than
+ * any before).  A CUDA graph captured from calls on this handle holds workspace pointers: it is valid only while the
+ * generation it was captured at is still current (deepclr_b200/models/stream.py re-captures on a mismatch). */
+int dclr_model_generation(const dclr_model *m);
 /*
  * Per-stage device timing with CUDA events recorded on the caller's stream (the reference times with an event pair
  * around predict: scripts/timing.py:32-47; this splits that interval by kernel stage).  When on, every
