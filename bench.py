@@ -3,8 +3,10 @@
   python bench.py [--gpus N --steps K --warmup W]            this repo's sm_100a path (C ABI, libdeepclr_b200.so)
   python bench.py --impl reference [...]                     the reference algorithm on the host cores (CPU oracle)
 
-One "step" = one forward over one batch of `--pairs` synthetic KITTI-shaped pairs per GPU (weak scaling: pairs are
-independent, every rank works on its own batch, no collective on the data path).  Prints ONE JSON line.
+One "step" = one forward over `--pairs` synthetic KITTI-shaped pairs.  Default = the configuration BASELINE.json quotes
+(configs[2]): 64 pairs IN TOTAL per step, sharded by pairs over the GPUs (strong scaling, 64/32/16/8 per GPU); the
+weak-scaling number (64 pairs per GPU) of the same run is reported beside it (`weak_scaling`).  Pairs are independent:
+no collective on the data path.  Prints ONE JSON line.
 """
 import argparse
 import json
@@ -31,7 +33,12 @@ def parse_args():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='native', choices=['native', 'reference'])
-    ap.add_argument('--pairs', type=int, default=64, help='pairs per GPU per step')
+    ap.add_argument('--pairs', type=int, default=64, help='pairs per step: in total (strong scaling) / per GPU (weak)')
+    ap.add_argument('--scaling', default='strong', choices=['strong', 'weak'],
+                    help='strong (default, BASELINE.json configs[2]): --pairs pairs in total sharded over the GPUs')
+    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU (0 = 2 when <= 32 pairs per GPU)')
+    ap.add_argument('--partial', action='store_true', help='ModelNet-shaped pairs with partial overlap (configs[3])')
+    ap.add_argument('--noise', type=float, default=0.02, help='ModelNet point noise sigma (0, 0.02, 0.04: the reference ladder)')
     ap.add_argument('--points', type=int, default=16384)
     ap.add_argument('--kind', default='kitti', choices=['kitti', 'modelnet'])
     ap.add_argument('--numerics', default=os.environ.get('DCLR_NUMERICS', 'fp16'), choices=['fp32', 'fp16', 'bf16'])
@@ -41,6 +48,12 @@ def parse_args():
     ap.add_argument('--raw-points', type=int, default=120000, help='mean points of a raw scan (KITTI HDL-64: ~120 k)')
     ap.add_argument('--cpu-pairs', type=int, default=40, help='pairs of the bounded CPU sample')
     return ap.parse_args()
+
+
+def workload_name(args, world):
+    if args.scaling == 'strong':
+        return f'{args.kind}_{args.points}pts_batch{args.pairs}_total_sharded_over_{world}_gpus'
+    return f'{args.kind}_{args.points}pts_batch{args.pairs}_per_gpu'
 
 
 def load_peaks():
@@ -64,13 +77,13 @@ def build_model_and_cfg(kind):
     return model, yaml.safe_load(open(path))
 
 
-def make_batches(kind, pairs, points, count, seed0):
+def make_batches(kind, pairs, points, count, seed0, **gen_kw):
     """`count` distinct [2*pairs, points, C] batches.  Generating 16k-point scans is slow in numpy, so a batch is
     assembled from a pool of seeded pairs; every batch is a different selection (no two identical inputs in a row)."""
     from deepclr_b200 import synth
     pool_n = min(pairs, 16)
     gen = synth.kitti_pair if kind == 'kitti' else synth.modelnet_pair
-    pool = [gen(seed0 + i, points)[:2] for i in range(pool_n)]
+    pool = [gen(seed0 + i, points, **gen_kw)[:2] for i in range(pool_n)]
     rng = np.random.default_rng(seed0)
     out = []
     for _ in range(count):
@@ -85,7 +98,7 @@ def make_batches(kind, pairs, points, count, seed0):
     return out
 
 
-STAGE_KERNEL = {'fps': 'fps_bucket_kernel', 'ball_query': 'bq_grid_query_kernel', 'knn': 'knn_fast_kernel',
+STAGE_KERNEL = {'fps': 'fps_tmem_kernel', 'ball_query': 'bq_grid_query_kernel', 'knn': 'knn_fast_kernel',
                 'flow_embed': 'flow_tc_kernel', 'pose_head_conv': 'head_tc_kernel', 'sa_mlp_maxpool': 'sa_mlp_kernel'}
 
 
@@ -224,17 +237,47 @@ def run_reference(args, rank, world):
     sample = f'{per_step} pair(s) of {args.points} points per step, batch 1 forwards'
     line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f'{args.kind}_{args.points}pts_batch{args.pairs}_per_gpu', 'sample': sample},
+            'higher_is_better': True, 'scaling': args.scaling, 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': workload_name(args, world), 'sample': sample},
             'cpu_baseline': {'value': value, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), file=RESULT, flush=True)
 
 
+def ref_cuda_pairs_per_s(kind, points, pairs, tf32, steps=5, warmup=2):
+    """Baseline B1: the reference's OWN CUDA kernels (oracle/_ref/libpointnet2_ref.so, compiled unmodified
+    from the reference tree for sm_100a) + torch fp32 dense layers (cuDNN / cuBLAS) = the reference forward as it runs
+    on this B200; kNN is a cdist + top-k STAND-IN (torch_cluster is not vendored).  Protocol of the reference's
+    scripts/timing.py:32-47: CUDA events around each forward, mean over the timed calls."""
+    import torch
+    from oracle import ref_cuda
+    torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
+    torch.backends.cudnn.allow_tf32 = bool(tf32)
+    model, cfg = build_model_and_cfg(kind)
+    sd = {k: v.cuda() for k, v in model.state_dict().items()}
+    xs = [torch.from_numpy(b).cuda() for b in make_batches(kind, pairs, points, 2, 1234)]
+    for i in range(warmup):
+        ref_cuda.forward(sd, cfg, xs[i % 2])
+    torch.cuda.synchronize()
+    times = []
+    for i in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ref_cuda.forward(sd, cfg, xs[i % 2])
+        b.record()
+        b.synchronize()
+        times.append(a.elapsed_time(b))
+    del sd, xs
+    torch.cuda.empty_cache()
+    return pairs / (sum(times) / len(times) * 1e-3)
+
+
 def run_native(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
+    from deepclr_b200 import sharding
+    from deepclr_b200.models import HostPipeline
     assert torch.cuda.is_available(), 'bench.py (native arm) needs a CUDA device: there is no CPU path'
     torch.cuda.set_device(local_rank)
     dev = torch.device('cuda', local_rank)
@@ -244,76 +287,137 @@ def run_native(args, rank, world, local_rank):
     model, _ = build_model_and_cfg(args.kind)
     model = model.to(dev)
     model.numerics = args.numerics
-    host = [torch.from_numpy(b).pin_memory() for b in make_batches(args.kind, args.pairs, args.points, ROTATE,
-                                                                   1234 + 1000 * rank)]
-    resident = [h.to(dev) for h in host]
-    B = args.pairs
+    twin = model.replica()
+    gen_kw = dict(partial=True, noise=args.noise) if args.kind == 'modelnet' and args.partial else \
+        (dict(noise=args.noise) if args.kind == 'modelnet' else {})
+    # strong scaling (BASELINE.json configs[2]): `--pairs` pairs IN TOTAL, contiguous shards of pairs
+    # (deepclr_b200.sharding.pair_range), 64/32/16/8 per GPU at 1/2/4/8 GPUs.  weak: `--pairs` per GPU.
+    b0, b1 = sharding.pair_range(args.pairs, world, rank)
+    share = {'strong': b1 - b0, 'weak': args.pairs}
+    assert min(share.values()) >= 1, 'more ranks than pairs'
+    full = [torch.from_numpy(b).pin_memory() for b in make_batches(args.kind, args.pairs, args.points, ROTATE,
+                                                                   1234 + 1000 * rank, **gen_kw)]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        """K steps between a barrier + synchronize on both sides, CUDA events on the launching stream; ms, max over ranks."""
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        e0.record()
-        for i in range(steps):
-            fn(i)
-        e1.record()
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- device-resident arm: inputs already in HBM
-    def step_resident(i):
-        with torch.no_grad():
-            return model(resident[i % ROTATE])[0]
+    def measure(B, steps, warmup):
+        """Resident and end-to-end throughput of this rank's B pairs per step.  <= 32 pairs per GPU: consecutive steps
+        alternate between two model replicas on two streams (the sampling kernel occupies one SM per cloud and is
+        latency-bound, so the step after it fills the rest of the GPU); every step still does all of its work."""
+        host = [h[torch.cat([torch.arange(B), args.pairs + torch.arange(B)])].contiguous().pin_memory() for h in full]
+        resident = [h.to(dev) for h in host]
+        lanes = args.streams if args.streams > 0 else (2 if B <= 32 else 1)
+        models = [model, twin][:lanes]
+        streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)] if lanes > 1 else [None]
+        cur = torch.cuda.current_stream(dev)
 
-    for i in range(args.warmup):
-        step_resident(i)
+        def run_resident(n):
+            for s in streams:
+                if s is not None:
+                    s.wait_stream(cur)
+            for i in range(n):
+                s = streams[i % lanes]
+                with torch.no_grad():
+                    if s is None:
+                        models[0](resident[i % ROTATE])
+                    else:
+                        with torch.cuda.stream(s):
+                            models[i % lanes](resident[i % ROTATE])
+            for s in streams:
+                if s is not None:
+                    cur.wait_stream(s)
+
+        run_resident(warmup)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        barrier()
+        if sampler:
+            sampler.start()
+        e0.record()
+        run_resident(steps)            # no per-stage events here: stage times come from a separate pass
+        e1.record()
+        barrier()
+        clocks = sampler.finish() if sampler else None
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        launches = sum(m_._native.last_launches() for m_ in models) * steps // lanes
+
+        # end to end through the public host-buffer API: H2D of every step's inputs from pinned memory and D2H of its poses
+        # inside the timed region (deepclr_b200.models.HostPipeline, forward replayed from CUDA graphs)
+        use_graph = os.environ.get('DCLR_GRAPH', '1') == '1'
+        pipe = HostPipeline(model, depth=2 * lanes, use_cuda_graph=use_graph, replicas=lanes)
+        pipe.run_all(host[i % ROTATE] for i in range(max(2 * lanes + 1, warmup // 2)))
+        pipe.h2d_bytes = pipe.d2h_bytes = 0
+        barrier()
+        e0.record()
+        outs = pipe.run_all(host[i % ROTATE] for i in range(steps))
+        e1.record()
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+        assert len(outs) == steps and all(torch.isfinite(o).all() for o in outs)
+        e2e = {'ms_per_step': ms_e2e / steps, 'h2d_bytes_per_step': pipe.h2d_bytes // steps,
+               'd2h_bytes_per_step': pipe.d2h_bytes // steps,
+               'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches%s%s)' % (
+                   ', forward replayed from CUDA graphs' if use_graph else '',
+                   ', 2 model replicas on 2 streams' if lanes > 1 else '')}
+        del pipe
+        return dict(B=B, ms=ms, ms_e2e=ms_e2e, e2e=e2e, clocks=clocks, launches=launches, resident=resident, host=host,
+                    lanes=lanes)
+
+    main = measure(share[args.scaling], args.steps, args.warmup)
+    B = main['B']
+    pairs_per_step = args.pairs if args.scaling == 'strong' else world * args.pairs
+    value = pairs_per_step * args.steps / (main['ms'] * 1e-3)
+    e2e = dict(main['e2e'], value=pairs_per_step * args.steps / (main['ms_e2e'] * 1e-3), unit='pairs/s')
+    other = None
+    if world > 1:                       # the other scaling mode, same run, reported beside the headline
+        o_mode = 'weak' if args.scaling == 'strong' else 'strong'
+        o = measure(share[o_mode], args.steps, args.warmup)
+        o_pairs = args.pairs if o_mode == 'strong' else world * args.pairs
+        other = {'scaling': o_mode, 'pairs_per_gpu_per_step': o['B'], 'value': o_pairs * args.steps / (o['ms'] * 1e-3),
+                 'ms_per_step': o['ms'] / args.steps, 'e2e_value': o_pairs * args.steps / (o['ms_e2e'] * 1e-3),
+                 'streams': o['lanes']}
+        del o
+    resident, host = main['resident'], main['host']
+
+    # ---- per-stage device times: a SECOND pass with CUDA events between the stages (dclr_model_set_timing), one stream
     native = model._native
     native.set_timing(True)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    ms = timed(step_resident, args.steps)
-    clocks = sampler.finish() if rank == 0 else None
+    with torch.no_grad():
+        for i in range(min(args.steps, 16)):
+            model(resident[i % ROTATE])
     stage_ms, calls = native.collect_timing()
     native.set_timing(False)
-    launches = native.last_launches() * args.steps
-    value = world * B * args.steps / (ms * 1e-3)
+    per_call = {k: v / max(calls, 1) for k, v in stage_ms.items()}
+    # genuine (centre, neighbour) rows of the last forward: what the grouped-MLP kernel really computes
+    M = native.npoint
+    sa_rows = int(sum(int(native.debug_tensor(1 + s, (2 * B, M)).clamp(min=1).sum().item())
+                      for s in range(len(native.nsamples))))
 
-    # ---- end-to-end arm: the public host-buffer API (deepclr_b200.models.HostPipeline): every step copies its inputs from
-    # pinned host memory and reads its poses back to the host inside the timed region; the copy of step i+1 is issued on
-    # a copy stream while step i computes (double-buffered device inputs), the host collects the poses of step i-1.
-    from deepclr_b200.models import HostPipeline
-    use_graph = os.environ.get('DCLR_GRAPH', '1') == '1'
-    pipe = HostPipeline(model, depth=2, use_cuda_graph=use_graph)
-    pipe.run_all(host[i % ROTATE] for i in range(max(3, args.warmup // 2)))
-    pipe.h2d_bytes = pipe.d2h_bytes = 0
-    e2e_out = []
-
-    def run_e2e(steps):
-        e2e_out.append(pipe.run_all(host[i % ROTATE] for i in range(steps)))
-
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # ---- plain pinned host -> device copies, all ranks at once: the box's H2D ceiling next to the e2e line
+    nbytes = host[0].numel() * 4
+    dst = torch.empty_like(resident[0])
+    for _ in range(3):
+        dst.copy_(host[0], non_blocking=True)
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    e0.record()
-    run_e2e(args.steps)
-    e1.record()
+    h0.record()
+    for i in range(20):
+        dst.copy_(host[i % ROTATE], non_blocking=True)
+    h1.record()
     barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_e2e = float(t.item())
-    assert len(e2e_out[0]) == args.steps and all(torch.isfinite(o).all() for o in e2e_out[0])
-    e2e = {'value': world * B * args.steps / (ms_e2e * 1e-3), 'unit': 'pairs/s',
-           'h2d_bytes_per_step': pipe.h2d_bytes // args.steps, 'd2h_bytes_per_step': pipe.d2h_bytes // args.steps,
-           'ms_per_step': ms_e2e / args.steps, 'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches%s)' % (', forward replayed from CUDA graphs' if use_graph else '')}
+    ms_h2d = max_over_ranks(h0.elapsed_time(h1))
+    h2d = {'gbps_per_rank': nbytes * 20 / (ms_h2d * 1e-3) / 1e9, 'gbps_all_ranks': world * nbytes * 20 / (ms_h2d * 1e-3) / 1e9,
+           'bytes_per_copy': nbytes, 'e2e_needs_gbps_all_ranks': world * e2e['h2d_bytes_per_step'] / (e2e['ms_per_step'] * 1e-3) / 1e9}
+    del dst
 
     # ---- raw-scan arm (SURVEY.md 8f rank 2): what the reference's inference loop does before its batch copy -- every
     # 2nd point, range filter, random subsample to N points, per scan in numpy on the host (transforms/build.py:37-39)
@@ -345,11 +449,8 @@ def run_native(args, rank, world, local_rank):
         raw_out = rpipe.run_all(raw[i % 2] for i in range(raw_steps))
         r1.record()
         barrier()
-        t = torch.tensor([r0.elapsed_time(r1)], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_raw = max_over_ranks(r0.elapsed_time(r1))
         assert len(raw_out) == raw_steps and all(torch.isfinite(o).all() for o in raw_out)
-        ms_raw = float(t.item())
         e2e_raw = {'value': world * B * raw_steps / (ms_raw * 1e-3), 'unit': 'pairs/s', 'steps': raw_steps,
                    'ms_per_step': ms_raw / raw_steps, 'h2d_bytes_per_step': rpipe.h2d_bytes // raw_steps,
                    'd2h_bytes_per_step': rpipe.d2h_bytes // raw_steps,
@@ -393,66 +494,115 @@ def run_native(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant stage (largest share of the step, timed live with CUDA events on the launch stream)
-    per_call = {k: v / max(calls, 1) for k, v in stage_ms.items()}
-    top = max(per_call, key=per_call.get)
-    flop_stage = {'flow_embed': 2700.1e6 if args.kind == 'kitti' else 2025.1e6,
-                  'pose_head_conv': 2149.1e6 if args.kind == 'kitti' else 1074.5e6,
-                  'sa_mlp_maxpool': 5234.4e6 if args.kind == 'kitti' else 1283.4e6}
-    C = 4 if args.kind == 'kitti' else 3
-    M, ns = (1024, (512, 1024)) if args.kind == 'kitti' else (512, (256, 512))
+    # ---- rooflines.  Per-stage times are those of the second (instrumented, single-stream) pass.
+    clocks = main['clocks']
+    step_ms = main['ms'] / args.steps
+    kitti = args.kind == 'kitti'
+    flop_stage = {'flow_embed': 2700.1e6 if kitti else 2025.1e6, 'pose_head_conv': 2149.1e6 if kitti else 1074.5e6,
+                  'sa_mlp_maxpool': 5234.4e6 if kitti else 1283.4e6}
+    C = 4 if kitti else 3
+    ns = (512, 1024) if kitti else (256, 512)
     G, N = 2 * B, args.points
-    bytes_stage = {'fps': G * (4 * C * N + 4 * M + 12 * M),
-                   'ball_query': G * (4 * C * N + 12 * M + 4 * M * sum(ns)),
-                   'knn': B * (12 * 2 * M + 4 * M * (20 if args.kind == 'kitti' else 30))}
-    if top in flop_stage:
-        ach = B * flop_stage[top] / (per_call[top] * 1e-3) / 1e12
-        roof = {'bound': 'tensor', 'achieved': ach, 'peak': peaks['tf'], 'unit': 'TFLOP/s', 'frac': ach / peaks['tf']}
-    else:
-        ach = bytes_stage.get(top, 0) / (per_call[top] * 1e-3) / 1e9
-        roof = {'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': ach / peaks['hbm']}
-    # every stage against its own roof (the dominant one is repeated in `roofline`): tensor stages in dense-equivalent
-    # TFLOP/s vs the sustained bf16 peak, the point ops in algorithmic GB/s vs the measured HBM peak
+    # algorithmic bytes per launch, SURVEY.md 8(d): FPS B(12 N + 4 npoint); ball query B(12 N + 12 M + 4 M ns) summed over
+    # the radii (one pass serves both); kNN 12 (Nx + Ny) + 16 Ny k per pair
+    bytes_stage = {'fps': G * (12 * N + 4 * M),
+                   'ball_query': G * (12 * N + 12 * M + 4 * M * sum(ns)),
+                   'knn': B * (12 * 2 * M + 16 * M * native.knn_k)}
+    sm_mhz = (clocks or {}).get('sm_mhz') or (clocks or {}).get('sm_max_mhz') or 1965.0
+    sm_max = (clocks or {}).get('sm_max_mhz') or 1965.0
+    ffma_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12                    # fp32 FFMA, TFLOP/s
+    sa_flop_row = 2.0 * (C * 16 + 16 * 16 + 16 * 32)
     roof_stages = {}
-    # dense-equivalent numerators the kernel does not actually perform (it skips the reference's padded duplicates /
-    # writes only genuine hits): reported, but no fraction of a hardware peak is claimed for them
-    dense_equiv_only = {'sa_mlp_maxpool': 'fp32 SIMT kernel, dense-equivalent flops (padded duplicate rows are skipped exactly)',
-                        'ball_query': 'dense-equivalent bytes (the reference writes fully padded index tensors)'}
     for k, t_ms in per_call.items():
         if t_ms <= 0:
             continue
-        if k in flop_stage:
+        if k in ('flow_embed', 'pose_head_conv'):
             v = B * flop_stage[k] / (t_ms * 1e-3) / 1e12
-            roof_stages[k] = {'bound': 'tensor', 'achieved': v, 'unit': 'TFLOP/s', 'frac': v / peaks['tf'], 'ms': t_ms}
+            roof_stages[k] = {'bound': 'tensor', 'achieved': v, 'unit': 'TFLOP/s', 'peak': peaks['tf'], 'frac': v / peaks['tf'],
+                              'ms': t_ms}
+        elif k == 'sa_mlp_maxpool':
+            actual = sa_rows * sa_flop_row / (t_ms * 1e-3) / 1e12
+            roof_stages[k] = {'bound': 'fp32 issue (SIMT)', 'achieved': actual, 'unit': 'TFLOP/s', 'peak': ffma_peak,
+                              'frac': actual / ffma_peak, 'ms': t_ms, 'rows_computed': sa_rows,
+                              'rows_dense_equivalent': G * M * sum(ns),
+                              'dense_equivalent_tflops': B * flop_stage[k] / (t_ms * 1e-3) / 1e12,
+                              'note': 'padded duplicate rows of the reference are skipped exactly; peak = 148 SMs x 128 FFMA '
+                                      'lanes x 2 x max SM clock'}
         elif k in bytes_stage:
             v = bytes_stage[k] / (t_ms * 1e-3) / 1e9
-            roof_stages[k] = {'bound': 'hbm', 'achieved': v, 'unit': 'GB/s', 'frac': v / peaks['hbm'], 'ms': t_ms}
-        if k in dense_equiv_only and k in roof_stages:
-            roof_stages[k].update(frac=None, bound='issue', note=dense_equiv_only[k])
-    roof.update({'kernel': top, 'traffic': ncu_traffic(top, args), 'peak_source': peaks['src'], 'ms_per_launch': per_call[top],
-                 'share_of_step': per_call[top] / (ms / args.steps)})
+            roof_stages[k] = {'bound': 'hbm', 'achieved': v, 'unit': 'GB/s', 'peak': peaks['hbm'], 'frac': v / peaks['hbm'],
+                              'ms': t_ms}
+    if 'fps' in roof_stages:
+        # serial rounds, one CTA per cloud: the meaningful figures are cycles per emitted sample and the SMs it occupies
+        roof_stages['fps'].update(bound='latency', cycles_per_sample=per_call['fps'] * 1e-3 * sm_mhz * 1e6 / max(M - 1, 1),
+                                  sms_occupied=min(G, 148), sm_count=148, hbm_frac=roof_stages['fps']['frac'],
+                                  note='dependent sampling rounds (up to 3 exact samples per round); HBM bytes are read once')
+    if 'ball_query' in roof_stages:
+        roof_stages['ball_query'].update(note='dense-equivalent bytes (the reference writes fully padded index tensors); the '
+                                              'fused path writes only genuine hits')
+    top = max((k for k in per_call if k in roof_stages), key=per_call.get)
+    roof = dict(roof_stages[top])
+    roof.update({'kernel': STAGE_KERNEL.get(top, top), 'stage': top, 'traffic': ncu_traffic(top, args), 'peak_source': peaks['src'],
+                 'ms_per_launch': per_call[top], 'share_of_step': per_call[top] / sum(per_call.values())})
+    tensor_flop = flop_stage['flow_embed'] + flop_stage['pose_head_conv']
+    per_gpu = value / world
+    roof_e2e = {'dense_equiv_frac': per_gpu * FLOP_PER_PAIR[args.kind] / 1e12 / peaks['tf'],
+                'actual_tensor_frac': per_gpu * tensor_flop / 1e12 / peaks['tf'], 'peak': peaks['tf'], 'unit': 'TFLOP/s',
+                'note': 'dense_equiv = the reference\'s 10.085 / 4.384 GFLOP per pair incl. padded SA rows; actual_tensor = '
+                        'flow + head GEMMs only (what the tensor pipe really computes)'}
 
     line = {'metric': METRIC, 'value': value, 'unit': 'pairs/s', 'n_gpus': world, 'steps': args.steps,
-            'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+            'warmup': args.warmup, 'ms_per_step': step_ms, 'higher_is_better': True, 'scaling': args.scaling,
             'vs_baseline': None, 'dtype': {'bf16': 'bf16', 'fp16': 'f16', 'fp32': 'f32'}[args.numerics], 'data': 'synthetic',
-            'config': {'workload': f'{args.kind}_{args.points}pts_batch{B}_per_gpu', 'pairs_per_gpu_per_step': B,
-                       'points_per_cloud': N, 'numerics': args.numerics, 'parallelism': f'dp{world} (independent pairs)',
+            'config': {'workload': workload_name(args, world),
+                       'pairs_per_step_all_gpus': pairs_per_step, 'pairs_per_gpu_per_step': B,
+                       'points_per_cloud': N, 'numerics': args.numerics, 'fps_tie_rule': native.fps_tie_rule,
+                       'parallelism': f'dp{world} (independent pairs, no collective on the data path)',
+                       'streams_per_gpu': main['lanes'],
+                       'partial_overlap': bool(args.partial), 'noise': args.noise if args.kind == 'modelnet' else None,
                        'l2': f'{ROTATE} distinct resident input batches cycled + >126 MB of per-step workspace traffic'},
-            'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof,
-            'stage_ms': per_call, 'roofline_stages': roof_stages,
+            'clocks': clocks, 'e2e': e2e, 'gpu_launches': main['launches'], 'roofline': roof,
+            'stage_ms': per_call, 'roofline_stages': roof_stages, 'roofline_e2e': roof_e2e, 'h2d_copy': h2d,
             'latency_b1': {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[int(len(lat) * 0.9)], 'n': len(lat),
                            'p50_graph_ms': lat_graph[len(lat_graph) // 2] if lat_graph else None,
                            'p90_graph_ms': lat_graph[int(len(lat_graph) * 0.9)] if lat_graph else None},
             'model_tflops': value * FLOP_PER_PAIR[args.kind] / 1e12}
+    if other is not None:
+        line[other['scaling'] + '_scaling'] = other
     if e2e_raw is not None:
         line['e2e_raw_scans'] = e2e_raw
+    if world > 1:
+        dist.destroy_process_group()
     if not args.no_cpu_baseline and world == 1:      # reported at N=1 only (rank 0 owns the host cores there)
+        del resident, host, full
+        torch.cuda.empty_cache()
+        # B1: the reference's own CUDA kernels + torch fp32 layers on this GPU (north_star target: >= 10x this)
+        try:
+            from oracle import ref_cuda
+            if ref_cuda.available():
+                b1 = {'what': 'reference CUDA ops (oracle/_ref, sm_100a rebuild of the unmodified reference sources) + torch '
+                              'fp32 dense layers; kNN = cdist + top-k stand-in; CUDA events per forward (scripts/timing.py:32-47)',
+                      'unit': 'pairs/s', 'runs': []}
+                for pairs_b1 in (1, 8, 64):
+                    for tf32 in (0, 1):
+                        try:
+                            v = ref_cuda_pairs_per_s(args.kind, args.points, pairs_b1, tf32)
+                            b1['runs'].append({'pairs_per_step': pairs_b1, 'tf32': bool(tf32), 'value': v})
+                        except RuntimeError as e:             # e.g. out of memory at batch 64 (grouped tensors are materialised)
+                            b1['runs'].append({'pairs_per_step': pairs_b1, 'tf32': bool(tf32), 'value': None,
+                                               'error': str(e).split('\n')[0][:120]})
+                            torch.cuda.empty_cache()
+                best = max((r['value'] for r in b1['runs'] if r['value']), default=None)
+                b1['best'] = best
+                b1['speedup_vs_best'] = value / best if best else None
+                b1['e2e_speedup_vs_best'] = e2e['value'] / best if best else None
+                line['b1_baseline'] = b1
+        except Exception as e:
+            line['b1_baseline'] = {'unavailable': f'{type(e).__name__}: {e}'[:200]}
         v, cores, dt = cpu_oracle_pairs_per_s(args.kind, args.points, args.cpu_pairs)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
                                 'sample': f'{args.cpu_pairs} batch-1 forwards of {N}-point pairs ({dt:.1f} s)'}
     print(json.dumps(line), file=RESULT, flush=True)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 RESULT = sys.stdout

@@ -376,6 +376,20 @@ class DeepCLR(BaseModel):
         return self._cloud_layers(x.transpose(1, 2))
 
     # ---- fused route
+    def replica(self) -> 'DeepCLR':
+        """An independent copy of the model (own parameters, own native handle and workspace): forwards of the original
+        and of a replica may overlap on different CUDA streams (one handle serialises its calls: include/deepclr_b200.h,
+        threading contract).  Used by HostPipeline(replicas=2) so that the latency-bound sampling of batch i+1 runs
+        beside the dense stages of batch i."""
+        import copy
+        native, key = self._native, self._native_key
+        self._native, self._native_key = None, None
+        try:
+            twin = copy.deepcopy(self)
+        finally:
+            self._native, self._native_key = native, key
+        return twin
+
     def graph_token(self, device: torch.device):
         """Identity of everything a CUDA graph captured from this model's fused forward points at: the native handle
         (rebuilt when parameters, numerics or the tie rule change) and its workspace generation (bumped when a larger

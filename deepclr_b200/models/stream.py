@@ -25,16 +25,25 @@ class HostPipeline:
     A yielded pose tensor is valid once the pipeline has moved `depth` batches on (or after `synchronize()`), the usual
     contract of a non-blocking copy; `run_all` returns fully synchronised results."""
 
-    def __init__(self, model, depth: int = 2, device: Optional[torch.device] = None, use_cuda_graph: bool = False):
+    def __init__(self, model, depth: int = 2, device: Optional[torch.device] = None, use_cuda_graph: bool = False,
+                 replicas: int = 1):
         """`use_cuda_graph`: the forward over each of the `depth` device input buffers is captured once per batch shape
-        and replayed (one graph launch per batch instead of ~11 kernel launches + the side-stream fork/join)."""
+        and replayed (one graph launch per batch instead of ~11 kernel launches + the side-stream fork/join).
+        `replicas` > 1: batch i runs on model replica i % replicas on its own compute stream (DeepCLR.replica()), so
+        consecutive batches overlap on the device -- the sampling kernel of a small batch occupies one SM per cloud for
+        ~0.4 ms and leaves the rest of the GPU to the dense stages of the batch before it.  Results are unchanged."""
         self.model = model
         self._use_graph = bool(use_cuda_graph)
         self._graphs: dict = {}
+        self.replicas = max(1, int(replicas))
         self.depth = max(2, int(depth))
+        if self.depth % self.replicas:
+            self.depth = self.replicas * ((self.depth + self.replicas - 1) // self.replicas)   # slot <-> replica is fixed
         self.device = device if device is not None else next(model.parameters()).device
         if self.device.type != 'cuda':
             raise RuntimeError('HostPipeline needs the model on a CUDA device: there is no CPU path')
+        self._models = [model] + [model.replica() for _ in range(self.replicas - 1)]
+        self._compute = [None] + [torch.cuda.Stream(device=self.device) for _ in range(self.replicas - 1)]
         self._copy = torch.cuda.Stream(device=self.device)
         self._in: List[Optional[torch.Tensor]] = [None] * self.depth
         self._out: List[Optional[torch.Tensor]] = [None] * (self.depth + 1)
@@ -56,7 +65,7 @@ class HostPipeline:
                 # block that kernels queued on the main stream still use, and the old buffer is released only once the
                 # forward that read it is done; the main stream is recorded as a user of the new block
                 buf = self._in[slot] = torch.empty(host.shape, dtype=torch.float32, device=self.device)
-                buf.record_stream(self._main())
+                buf.record_stream(self._compute[slot % self.replicas] or self._main())
             buf.copy_(host, non_blocking=True)
             self._loaded[slot].record(self._copy)
         self._used[slot] = True
@@ -67,20 +76,21 @@ class HostPipeline:
 
     def _forward(self, slot: int) -> torch.Tensor:
         x = self._in[slot]
+        model = self._models[slot % self.replicas]
         if not self._use_graph:
-            return self.model(x)[0]
-        key = (slot, x.data_ptr(), tuple(x.shape), _graph_token(self.model, self.device))
+            return model(x)[0]
+        key = (slot, x.data_ptr(), tuple(x.shape), _graph_token(model, self.device))
         hit = self._graphs.get(slot)
         if hit is None or hit[0] != key:
             # first batch of this shape in this slot: run it directly (this also sizes the native workspace), then
             # capture the same call over the slot's own buffer -- the graph reads whatever the copy stream puts there
-            y = self.model(x)[0]
+            y = model(x)[0]
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, capture_error_mode='thread_local'):   # other threads (NCCL watchdog) may call CUDA
-                y_static = self.model(x)[0]
+                y_static = model(x)[0]
             # the capture itself may have grown the workspace of ANOTHER slot's shape: key on the token after it
-            key = key[:3] + (_graph_token(self.model, self.device),)
+            key = key[:3] + (_graph_token(model, self.device),)
             self._graphs[slot] = (key, g, y_static)
             return y
         hit[1].replay()
@@ -98,15 +108,18 @@ class HostPipeline:
             nxt = next(it, None)
             if nxt is not None:
                 self._stage((i + 1) % self.depth, nxt)
-            main.wait_event(self._loaded[slot])
-            with torch.no_grad():
-                y = self._forward(slot)
-            self._freed[slot].record(main)
+            cs = self._compute[slot % self.replicas] or main          # this batch's compute stream
+            if cs is not main and i < self.replicas:
+                cs.wait_stream(main)                                  # work queued before run() comes first
+            cs.wait_event(self._loaded[slot])
             o = i % (self.depth + 1)
-            if self._out[o] is None or self._out[o].shape != y.shape:
-                self._out[o] = torch.empty(y.shape, dtype=y.dtype).pin_memory()
-            self._out[o].copy_(y, non_blocking=True)
-            self._done[o].record(main)
+            with torch.cuda.stream(cs), torch.no_grad():
+                y = self._forward(slot)
+                self._freed[slot].record(cs)
+                if self._out[o] is None or self._out[o].shape != y.shape:
+                    self._out[o] = torch.empty(y.shape, dtype=y.dtype).pin_memory()
+                self._out[o].copy_(y, non_blocking=True)
+                self._done[o].record(cs)
             self.d2h_bytes += y.numel() * y.element_size()
             i += 1
             yield self._out[o]
@@ -127,7 +140,8 @@ class HostPipeline:
 
     def synchronize(self) -> None:
         self._copy.synchronize()
-        torch.cuda.current_stream(self.device).synchronize()
+        for cs in self._compute:
+            (cs or torch.cuda.current_stream(self.device)).synchronize()
 
 
 class RawScanPipeline(HostPipeline):

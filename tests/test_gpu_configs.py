@@ -1,0 +1,134 @@
+"""GPU parity at the configurations BASELINE.json names, beyond the committed goldens ("weak" 3):
+  * a B = 16 batch of full-size KITTI-shaped pairs against the oracle run on the spot -- the persistent tcgen05 kernels
+    walk several waves of tiles per CTA there and pool with atomicMax, which the B <= 2 goldens never exercise;
+  * a ModelNet40-shaped pair with partial overlap (configs[3]): a visible share of the flow-embedding rows is
+    radius-masked (deepclr/models/deepclr.py:220-223);
+  * cloud_features(x, m) with an augmentation matrix (deepclr.py:512-514, tgm.transform_points);
+  * the stage-level C entries (dclr_sa_msg_fused / dclr_flow_embed_fused / dclr_pose_head_fused) against the whole path;
+  * CUDA graphs that outlive a workspace re-allocation or a weight update.
+Tolerances are those of tests/test_gpu_model.py."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle
+from tests.test_gpu_model import TOL, _check_against, _modes
+from tests.util import build_from_golden, load_golden
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def _live(kind, dbg, y_ref):
+    return dict(kind=np.array(kind), fps_idx=dbg['fps_idx'], ball_cnt0=dbg['ball_cnt0'], ball_cnt1=dbg['ball_cnt1'],
+                knn_idx=dbg['knn_idx'], cloud_feat=dbg['cloud_feat'], motion_feat=dbg['motion_feat'], y=y_ref)
+
+
+def test_forward_matches_oracle_at_batch_16_full_size():
+    from deepclr_b200 import synth
+    g = load_golden('kitti_b1')
+    model, cfg = build_from_golden(g, DEV)
+    sd = {k: v.cpu() for k, v in model.state_dict().items()}
+    x_np = synth.batch('kitti', 16, 700)
+    dbg = {}
+    y_ref = model_oracle.forward(sd, cfg, torch.from_numpy(x_np), debug=dbg).numpy()
+    for mode in _modes():
+        _check_against(_live('kitti', dbg, y_ref), model, x_np, mode)
+
+
+@pytest.mark.parametrize('noise', [0.0, 0.02, 0.04])
+def test_partial_overlap_modelnet_pairs(noise):
+    from deepclr_b200 import synth
+    g = load_golden('modelnet_b2')
+    model, cfg = build_from_golden(g, DEV)
+    sd = {k: v.cpu() for k, v in model.state_dict().items()}
+    x_np = synth.batch('modelnet', 3, 40, partial=True, noise=noise)
+    dbg = {}
+    y_ref = model_oracle.forward(sd, cfg, torch.from_numpy(x_np), debug=dbg).numpy()
+    # how many (template sample, neighbour) rows lie outside the merge radius: the crop must make the mask matter
+    B, M = 3, dbg['cloud_feat'].shape[2]
+    xyz = dbg['cloud_feat'][:, :3].transpose(0, 2, 1).reshape(-1, 3)            # [2B*M, 3] rows, templates first
+    row, col = dbg['knn_idx'][0], dbg['knn_idx'][1]
+    dist = np.linalg.norm(xyz[B * M + col] - xyz[row], axis=1)
+    radius = float(cfg['params']['merge']['params']['radius'])
+    masked = float((dist >= radius).mean())
+    assert masked > 0.02, f'only {masked:.3%} of the rows are radius-masked'
+    for mode in _modes():
+        _check_against(_live('modelnet', dbg, y_ref), model, x_np, mode)
+
+
+def test_cloud_features_with_augmentation_matrix():
+    """`m` [2B,4,4] moves every cloud before the set abstraction, in place, as tgm.transform_points(m, xyz) does
+    (homogeneous 4x4; rigid here, so no perspective divide); everything after it must equal the oracle on the moved cloud."""
+    from deepclr_b200 import synth
+    g = load_golden('kitti_small_b2')
+    model, cfg = build_from_golden(g, DEV)
+    sd = {k: v.cpu() for k, v in model.state_dict().items()}
+    x_np = synth.batch('kitti', 2, 77, n=int(g['n']))
+    rng = np.random.default_rng(5)
+    m_np = np.stack([synth.random_motion(rng, 2.0, 10.0) for _ in range(4)])
+    x = torch.from_numpy(x_np.copy()).to(DEV)
+    m = torch.from_numpy(m_np).float().to(DEV)
+    with torch.no_grad():
+        feat = model.cloud_features(x, m=m)
+    moved = x.cpu().numpy()                                        # the reference transforms x in place (deepclr.py:514)
+    want_xyz = np.einsum('bij,bnj->bni', m_np[:, :3, :3], x_np[:, :, :3].astype(np.float64)) + m_np[:, None, :3, 3]
+    np.testing.assert_allclose(moved[:, :, :3], want_xyz, rtol=0, atol=2e-5)
+    np.testing.assert_array_equal(moved[:, :, 3], x_np[:, :, 3])
+    dbg = {}
+    ref = model_oracle.cloud_features(sd, cfg['params'], torch.from_numpy(moved), debug=dbg).numpy()
+    got = feat.cpu().numpy()
+    assert np.array_equal(got[:, :3], ref[:, :3])
+    assert np.abs(got - ref).max() <= 1e-4 * np.abs(ref[:, 3:]).max()
+
+
+def test_stage_level_entries_equal_the_whole_path():
+    from deepclr_b200 import synth
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    x = torch.from_numpy(synth.batch('kitti', 3, 90, n=int(g['n']))).to(DEV)
+    for mode in _modes():
+        model.numerics = mode
+        with torch.no_grad():
+            model(x)
+            native = model._native
+            y, feat, motion = native.forward_pairs(x, want_feat=True, want_motion=True)
+            assert native.workspace_bytes(6, int(g['n'])) > 0
+            new_xyz = feat[:, :3].transpose(1, 2).contiguous()
+            sa = native.sa_msg(x, new_xyz)
+            assert torch.equal(sa, feat[:, 3:])
+            emb = native.flow_embed(feat)
+            assert torch.equal(emb[:, :3], motion[:, :3])
+            tol = 1e-6 if mode == 'fp32' else TOL[mode]['feat'] * 0.1
+            assert float((emb - motion).abs().max()) <= tol * float(motion[:, 3:].abs().max())
+            y2 = native.pose_head(motion)
+            np.testing.assert_allclose(y2.cpu().numpy(), y.cpu().numpy(), atol=2e-3 if mode != 'fp32' else 1e-6)
+
+
+def test_graphs_survive_workspace_growth_and_weight_updates():
+    """A graph captured for a small shape, then a larger shape grows the native workspace (the old one is freed), then
+    the small graph is used again: it must notice (dclr_model_generation) and re-capture instead of replaying kernels
+    that point into freed memory.  Same after the parameters change (the native handle is rebuilt)."""
+    from deepclr_b200 import synth
+    from deepclr_b200.models import GraphedForward, ModelInferenceHelper
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    small = [torch.from_numpy(synth.batch('kitti', 1, 800 + i, n=1024)).to(DEV) for i in range(2)]
+    big = [torch.from_numpy(synth.batch('kitti', 2, 810 + i, n=4096)).to(DEV) for i in range(2)]
+    helper = ModelInferenceHelper(model, use_cuda_graph=True)
+    plain = ModelInferenceHelper(model)
+    for rounds in range(2):
+        for xs in (small, big, small):
+            for x in xs:
+                assert torch.equal(helper.predict(x[-1], x[0]), plain.predict(x[-1], x[0]))
+    gf = GraphedForward(model, small[0])
+    first = gf.captures
+    with torch.no_grad():
+        model(torch.from_numpy(synth.batch('kitti', 4, 820, n=8192)).to(DEV))       # grows the workspace
+        want = model(small[1])[0].clone()
+    assert torch.equal(gf(small[1]), want) and gf.captures == first + 1
+    with torch.no_grad():
+        for p in model.parameters():
+            p.mul_(1.01)
+        want = model(small[0])[0].clone()
+    assert torch.equal(gf(small[0]), want) and gf.captures == first + 2
