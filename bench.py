@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument('--pairs', type=int, default=64, help='pairs per step: in total (strong scaling) / per GPU (weak)')
     ap.add_argument('--scaling', default='strong', choices=['strong', 'weak'],
                     help='strong (default, BASELINE.json configs[2]): --pairs pairs in total sharded over the GPUs')
-    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU (0 = 2 when <= 32 pairs per GPU)')
+    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU: 1 or 2 (default 2)')
     ap.add_argument('--partial', action='store_true', help='ModelNet-shaped pairs with partial overlap (configs[3])')
     ap.add_argument('--noise', type=float, default=0.02, help='ModelNet point noise sigma (0, 0.02, 0.04: the reference ladder)')
     ap.add_argument('--points', type=int, default=16384)
@@ -310,12 +310,13 @@ def run_native(args, rank, world, local_rank):
         return float(t.item())
 
     def measure(B, steps, warmup):
-        """Resident and end-to-end throughput of this rank's B pairs per step.  <= 32 pairs per GPU: consecutive steps
-        alternate between two model replicas on two streams (the sampling kernel occupies one SM per cloud and is
-        latency-bound, so the step after it fills the rest of the GPU); every step still does all of its work."""
+        """Resident and end-to-end throughput of this rank's B pairs per step.  Consecutive steps alternate between two
+        model replicas on two streams (--streams 1: one): the sampling kernel occupies one SM per cloud and is latency-
+        bound, so the dense stages of the step before it fill the rest of the GPU; every step still does all of its work
+        (measured on one B200, resident pairs/s with 1 | 2 streams: 64 pairs 55.0 k | 64.1 k, 8 pairs 12.8 k | 23.6 k)."""
         host = [h[torch.cat([torch.arange(B), args.pairs + torch.arange(B)])].contiguous().pin_memory() for h in full]
         resident = [h.to(dev) for h in host]
-        lanes = args.streams if args.streams > 0 else (2 if B <= 32 else 1)
+        lanes = min(2, args.streams) if args.streams > 0 else 2
         models = [model, twin][:lanes]
         streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)] if lanes > 1 else [None]
         cur = torch.cuda.current_stream(dev)

@@ -73,7 +73,7 @@ def test_cloud_features_with_augmentation_matrix():
         feat = model.cloud_features(x, m=m)
     moved = x.cpu().numpy()                                        # the reference transforms x in place (deepclr.py:514)
     want_xyz = np.einsum('bij,bnj->bni', m_np[:, :3, :3], x_np[:, :, :3].astype(np.float64)) + m_np[:, None, :3, 3]
-    np.testing.assert_allclose(moved[:, :, :3], want_xyz, rtol=0, atol=2e-5)
+    np.testing.assert_allclose(moved[:, :, :3], want_xyz, rtol=1e-5, atol=1e-4)      # fp32 matmul of ~80 m coordinates
     np.testing.assert_array_equal(moved[:, :, 3], x_np[:, :, 3])
     dbg = {}
     ref = model_oracle.cloud_features(sd, cfg['params'], torch.from_numpy(moved), debug=dbg).numpy()
