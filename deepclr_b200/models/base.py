@@ -40,9 +40,10 @@ class ModelInferenceHelper:
     features; clouds of different size are randomly sub-sampled to the smaller one."""
 
     def __init__(self, model: BaseModel, is_sequential: bool = False, use_cuda_graph: bool = False):
-        """`use_cuda_graph` (not in the reference): pairwise predictions of CUDA clouds replay the forward from a CUDA
-        graph captured per input shape (GraphedForward; 0.65 instead of 0.76 ms per KITTI pair) -- for streams of
-        equally sized clouds, e.g. after the device-side subsample."""
+        """`use_cuda_graph` (not in the reference): predictions of CUDA clouds replay the work from a CUDA graph captured
+        per input shape -- pairwise: the whole forward (GraphedForward); sequential: the per-frame step = set abstraction
+        of the new scan + merge/output against the cached features + cache update (GraphedSequentialStep) -- for streams
+        of equally sized clouds, e.g. after the device-side subsample."""
         self._model = model
         self._input_dim = model.get_input_dim()
         self._model.eval()
@@ -50,12 +51,15 @@ class ModelInferenceHelper:
         self._state: Optional[torch.Tensor] = None
         self._use_graph = bool(use_cuda_graph)
         self._graphs: Dict = {}
+        self._seq_graph = None                       # GraphedSequentialStep of the current cloud shape
 
     def has_state(self) -> bool:
-        return self._state is not None
+        return self._state is not None or (self._seq_graph is not None and self._seq_graph._has_prev)
 
     def reset_state(self) -> None:
         self._state = None
+        if self._seq_graph is not None:
+            self._seq_graph.reset()
 
     def _fit_dim(self, cloud: torch.Tensor, what: str) -> torch.Tensor:
         if cloud.shape[1] > self._input_dim:
@@ -74,6 +78,18 @@ class ModelInferenceHelper:
             if self._is_sequential:
                 if template is not None:
                     raise RuntimeError("Only the source cloud is required for sequential prediction.")
+                if self._use_graph and source.is_cuda:
+                    from .stream import GraphedSequentialStep
+                    sg = self._seq_graph
+                    if sg is None or tuple(sg.static_x.shape[1:]) != tuple(source.shape):
+                        carry = None
+                        if sg is not None and sg._has_prev:       # a new cloud size mid-sequence: keep the cached features
+                            carry = sg._prev
+                        sg = self._seq_graph = GraphedSequentialStep(self._model, source)
+                        if carry is not None:
+                            sg._prev, sg._has_prev = carry.clone(), True
+                    y = sg.step(source)
+                    return None if y is None else y[0, :].clone()
                 feat = self._model.cloud_features(source.unsqueeze(0))[0, ...]
                 previous, self._state = self._state, feat
                 if previous is None:

@@ -22,19 +22,11 @@ from ..config.config import Config
 from ..data.labels import LabelType
 from ..pointnet2 import PointnetSAModuleMSG
 from ..torch_cluster import knn
-from ..utils.factory import factory
-from ..utils.metrics import trans_loss, rot_loss
 from .base import BaseModel
+from .compat_losses import (AccumulatedLoss, DeepCLRLoss, DeepCLRModule, TransformLoss,  # noqa: F401
+                            TransformLossCalculation, TransformUncertaintyLoss, make_loss_layer, make_module, split_output)
 from .helper import Conv1dMultiLayer, LinearMultiLayer
 from .native import NativeModel
-
-
-class DeepCLRModule(nn.Module, metaclass=abc.ABCMeta):
-    """Base class of the configurable sub-modules (looked up by class name)."""
-
-    @abc.abstractmethod
-    def output_dim(self) -> int:
-        raise NotImplementedError
 
 
 def split_features(x: torch.Tensor) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
@@ -203,102 +195,6 @@ class OutputSimple(DeepCLRModule):
         return self._output_activation(self.output(self.linear(x)))
 
 
-class TransformLossCalculation(nn.Module):
-    """(translation loss, rotation loss) with the reference's NaN/Inf guard (deepclr.py:297-341)."""
-
-    def __init__(self, label_type: LabelType, p: int, reduction: Optional[str] = 'mean'):
-        super().__init__()
-        self._label_type, self._p, self._reduction = label_type, p, reduction
-
-    def forward(self, y_pred: torch.Tensor, y: torch.Tensor):
-        both = torch.cat((trans_loss(y_pred, y, self._label_type, p=self._p, reduction='none'),
-                          rot_loss(y_pred, y, self._label_type, p=self._p, reduction='none')), dim=1)
-        if self._reduction == 'mean':
-            both = torch.mean(both, dim=0)
-        if not bool(torch.isfinite(both).all()):
-            raise RuntimeError("TransformLoss: loss is nan or inf:\ny_pred = \n{}\ny = \n{}".format(y_pred, y))
-        return (both[0], both[1]) if self._reduction == 'mean' else both
-
-
-class DeepCLRLoss(DeepCLRModule, metaclass=abc.ABCMeta):
-    def output_dim(self) -> int:
-        return 1
-
-    @abc.abstractmethod
-    def get_weights(self) -> Dict:
-        raise NotImplementedError
-
-
-class TransformLoss(DeepCLRLoss):
-    """sx * translation + sq * rotation, fixed weights."""
-
-    def __init__(self, label_type: LabelType, p: int, sx: float, sq: float, **_kwargs: Any):
-        super().__init__()
-        self._transform_loss = TransformLossCalculation(label_type, p, reduction='mean')
-        self._sx, self._sq = sx, sq
-
-    def get_weights(self) -> Dict:
-        return {}
-
-    def forward(self, y_pred, y, **kwargs: Any) -> torch.Tensor:
-        p_loss, q_loss = self._transform_loss(y_pred, y)
-        return p_loss * self._sx + q_loss * self._sq
-
-
-class TransformUncertaintyLoss(DeepCLRLoss):
-    """Homoscedastic-uncertainty weighting with learnable sx, sq."""
-
-    def __init__(self, label_type: LabelType, p: int, sx: float, sq: float, **_kwargs: Any):
-        super().__init__()
-        self._transform_loss = TransformLossCalculation(label_type, p, reduction='mean')
-        self._sx = torch.nn.Parameter(torch.Tensor([sx]))
-        self._sq = torch.nn.Parameter(torch.Tensor([sq]))
-
-    def get_weights(self) -> Dict:
-        return {'sx': self._sx.item(), 'sq': self._sq.item()}
-
-    def forward(self, y_pred, y, **kwargs: Any) -> torch.Tensor:
-        p_loss, q_loss = self._transform_loss(y_pred, y)
-        return p_loss * torch.exp(-self._sx) + self._sx + q_loss * torch.exp(-self._sq) + self._sq
-
-
-class AccumulatedLoss(DeepCLRLoss):
-    def __init__(self, modules: List[torch.nn.Module]):
-        super().__init__()
-        self.loss_list = torch.nn.ModuleList(modules)
-
-    def get_weights(self) -> Dict:
-        weights: Dict = {}
-        for loss in self.loss_list:
-            for key, value in loss.get_weights().items():
-                if key in weights:
-                    raise RuntimeError("Duplicate loss keys")
-                weights[key] = value
-        return weights
-
-    def forward(self, *args: Any) -> torch.Tensor:
-        return torch.stack([loss(*args) for loss in self.loss_list], dim=0).sum()
-
-
-def init_module(cfg: Config, *args: Any, **kwargs: Any) -> DeepCLRModule:
-    return factory(DeepCLRModule, cfg.name, *args, **cfg.params, **kwargs)
-
-
-def init_loss_module(cfg: Config, label_type: LabelType, *args: Any, **kwargs: Any) -> DeepCLRLoss:
-    return factory(DeepCLRLoss, cfg.name, *args, label_type=label_type, **cfg.params, **kwargs)
-
-
-def init_optional_module(cfg: Optional[Config], *args: Any, **kwargs: Any) -> Optional[DeepCLRModule]:
-    return None if cfg is None else factory(DeepCLRModule, cfg.name, *args, **cfg.params, **kwargs)
-
-
-def split_output(output: Any) -> Tuple[Any, Any]:
-    if isinstance(output, (list, tuple)):
-        assert len(output) == 2
-        return output[0], output[1]
-    return output, dict()
-
-
 def _as_cfg(c: Union[Config, dict, None]) -> Optional[Config]:
     if c is None or isinstance(c, Config):
         return c
@@ -315,20 +211,16 @@ class DeepCLR(BaseModel):
         self._input_dim = input_dim
         self._label_type = label_type
         cloud_features, merge, output, transform = map(_as_cfg, (cloud_features, merge, output, transform))
-        transform_layer = init_optional_module(transform, input_dim=input_dim, **kwargs)
+        transform_layer = None if transform is None else make_module(DeepCLRModule, transform, input_dim=input_dim, **kwargs)
         feat_in = input_dim if transform_layer is None else transform_layer.output_dim()
-        cloud_feat_layer = init_module(cloud_features, input_dim=feat_in, **kwargs)
-        merge_layer = init_module(merge, input_dim=cloud_feat_layer.output_dim(), **kwargs)
-        output_layer = init_module(output, input_dim=merge_layer.output_dim(), label_type=label_type, **kwargs)
+        cloud_feat_layer = make_module(DeepCLRModule, cloud_features, input_dim=feat_in, **kwargs)
+        merge_layer = make_module(DeepCLRModule, merge, input_dim=cloud_feat_layer.output_dim(), **kwargs)
+        output_layer = make_module(DeepCLRModule, output, input_dim=merge_layer.output_dim(), label_type=label_type,
+                                   **kwargs)
         self._cloud_layers = nn.Sequential(cloud_feat_layer) if transform_layer is None \
             else nn.Sequential(transform_layer, cloud_feat_layer)
         self._merge_layers = nn.Sequential(merge_layer, output_layer)
-        if loss is None:
-            self._loss_layer = None
-        elif isinstance(loss, list):
-            self._loss_layer = AccumulatedLoss([init_loss_module(_as_cfg(c), label_type, **kwargs) for c in loss])
-        else:
-            self._loss_layer = init_loss_module(_as_cfg(loss), label_type, **kwargs)
+        self._loss_layer = make_loss_layer(loss, label_type, _as_cfg, **kwargs)
         # fused route state
         self.numerics = os.environ.get('DCLR_NUMERICS', 'fp32')   # 'fp32' | 'fp16' | 'bf16' (include/deepclr_b200.h)
         self.fps_tie_rule: Optional[str] = None    # None = deepclr_b200.get_fps_tie_rule() at call time ('reference')

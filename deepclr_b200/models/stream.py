@@ -254,3 +254,66 @@ class GraphedForward:
             raise ValueError(f'graph captured for {tuple(self.static_x.shape)}, got {tuple(x.shape)}')
         self.static_x.copy_(x, non_blocking=True)
         return self.replay()
+
+
+class GraphedSequentialStep:
+    """One frame of sequential (odometry) prediction as a single CUDA-graph launch: set abstraction of the new scan,
+    merge + output against the cached features of the previous frame, and the cache update -- the per-frame step of
+    ModelInferenceHelper(is_sequential=True) (deepclr/models/base.py:97-112, driver loop scripts/inference.py:83-119).
+    `step(cloud)` returns the pose of `cloud` against the previous one (a static buffer: clone to keep), None for the
+    first frame.  One instance per cloud shape; a different shape or `reset()` starts a new sequence."""
+
+    def __init__(self, model, example: torch.Tensor):
+        dev = next(model.parameters()).device
+        if dev.type != 'cuda':
+            raise RuntimeError('GraphedSequentialStep needs the model on a CUDA device: there is no CPU path')
+        self.model, self._dev = model, dev
+        self.static_x = torch.empty((1,) + tuple(example.shape), dtype=torch.float32, device=dev)
+        self.static_x[0].copy_(example)
+        self._prev: Optional[torch.Tensor] = None
+        self._has_prev = False
+        self.graph = None
+        self._token = None
+
+    def reset(self) -> None:
+        self._has_prev = False
+
+    def _body(self):
+        feat = self.model.cloud_features(self.static_x)                  # [1, 3+F, npoint]
+        y = self.model.forward(torch.cat((self._prev, feat), 0), is_feat=True)[0]
+        self._prev.copy_(feat)
+        return y
+
+    def _capture(self) -> None:
+        keep = self._prev.clone()
+        side = torch.cuda.Stream(device=self._dev)
+        side.wait_stream(torch.cuda.current_stream(self._dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(2):                   # sizes the native workspace; the cache is restored below
+                self._body()
+        torch.cuda.current_stream(self._dev).wait_stream(side)
+        torch.cuda.synchronize(self._dev)
+        x_keep = self.static_x.clone()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode='thread_local'), torch.no_grad():
+            self.static_y = self._body()
+        self._prev.copy_(keep)
+        self.static_x.copy_(x_keep)
+        self._token = _graph_token(self.model, self._dev)
+
+    def step(self, cloud: torch.Tensor) -> Optional[torch.Tensor]:
+        if tuple(cloud.shape) != tuple(self.static_x.shape[1:]):
+            raise ValueError(f'graph captured for {tuple(self.static_x.shape[1:])}, got {tuple(cloud.shape)}')
+        self.static_x[0].copy_(cloud, non_blocking=True)
+        if not self._has_prev:
+            with torch.no_grad():
+                feat = self.model.cloud_features(self.static_x)
+            if self._prev is None:
+                self._prev = torch.empty_like(feat)
+            self._prev.copy_(feat)
+            self._has_prev = True
+            return None
+        if self.graph is None or _graph_token(self.model, self._dev) != self._token:
+            self._capture()
+        self.graph.replay()
+        return self.static_y

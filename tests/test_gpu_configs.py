@@ -134,3 +134,25 @@ def test_graphs_survive_workspace_growth_and_weight_updates():
             p.mul_(1.01)
         want = model(small[0])[0].clone()
     assert torch.equal(gf(small[0]), want) and gf.captures == first + 2
+
+
+def test_sequential_mode_with_cuda_graph_equals_plain():
+    """Odometry mode (deepclr/models/base.py:97-112): the per-frame step replayed from one CUDA graph gives the poses of
+    the plain per-frame calls, over a sequence that changes its cloud size midway and is reset once."""
+    from deepclr_b200 import synth
+    from deepclr_b200.models import ModelInferenceHelper
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    frames = [torch.from_numpy(synth.kitti_pair(900 + i, 2048 if i < 5 else 3000)[i % 2]).to(DEV) for i in range(8)]
+    plain = ModelInferenceHelper(model, is_sequential=True)
+    graphed = ModelInferenceHelper(model, is_sequential=True, use_cuda_graph=True)
+    for rep in range(2):
+        for f in frames:
+            a, b = plain.predict(f), graphed.predict(f)
+            assert (a is None) == (b is None)
+            if a is not None:
+                assert torch.equal(a, b)
+            assert plain.has_state() and graphed.has_state()
+        plain.reset_state()
+        graphed.reset_state()
+        assert not graphed.has_state()

@@ -54,6 +54,10 @@ def main():
         p50, p90 = run(helper, frames)
         print(json.dumps({'mode': 'sequential', 'points_per_frame': n, 'input': 'device-resident frames',
                           'p50_ms': p50, 'p90_ms': p90, 'frames': 30}), flush=True)
+        graphed = ModelInferenceHelper(model, is_sequential=True, use_cuda_graph=True)
+        p50, p90 = run(graphed, frames)
+        print(json.dumps({'mode': 'sequential, per-frame step replayed from one CUDA graph', 'points_per_frame': n,
+                          'input': 'device-resident frames', 'p50_ms': p50, 'p90_ms': p90, 'frames': 30}), flush=True)
     raw = [torch.from_numpy(scan(rng, int(rng.integers(115000, 125000)))).pin_memory() for _ in range(35)]
 
     def prep(host):
