@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument('--pairs', type=int, default=64, help='pairs per step: in total (strong scaling) / per GPU (weak)')
     ap.add_argument('--scaling', default='strong', choices=['strong', 'weak'],
                     help='strong (default, BASELINE.json configs[2]): --pairs pairs in total sharded over the GPUs')
-    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU: 1 or 2 (default 2)')
+    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU (default 2)')
     ap.add_argument('--partial', action='store_true', help='ModelNet-shaped pairs with partial overlap (configs[3])')
     ap.add_argument('--noise', type=float, default=0.02, help='ModelNet point noise sigma (0, 0.02, 0.04: the reference ladder)')
     ap.add_argument('--points', type=int, default=16384)
@@ -287,7 +287,7 @@ def run_native(args, rank, world, local_rank):
     model, _ = build_model_and_cfg(args.kind)
     model = model.to(dev)
     model.numerics = args.numerics
-    twin = model.replica()
+    replicas = [model] + [model.replica() for _ in range(max(2, args.streams) - 1)]
     gen_kw = dict(partial=True, noise=args.noise) if args.kind == 'modelnet' and args.partial else \
         (dict(noise=args.noise) if args.kind == 'modelnet' else {})
     # strong scaling (BASELINE.json configs[2]): `--pairs` pairs IN TOTAL, contiguous shards of pairs
@@ -316,8 +316,8 @@ def run_native(args, rank, world, local_rank):
         (measured on one B200, resident pairs/s with 1 | 2 streams: 64 pairs 55.0 k | 64.1 k, 8 pairs 12.8 k | 23.6 k)."""
         host = [h[torch.cat([torch.arange(B), args.pairs + torch.arange(B)])].contiguous().pin_memory() for h in full]
         resident = [h.to(dev) for h in host]
-        lanes = min(2, args.streams) if args.streams > 0 else 2
-        models = [model, twin][:lanes]
+        lanes = args.streams if args.streams > 0 else 2
+        models = replicas[:lanes]
         streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)] if lanes > 1 else [None]
         cur = torch.cuda.current_stream(dev)
 

@@ -222,7 +222,12 @@ class DeepCLR(BaseModel):
         self._merge_layers = nn.Sequential(merge_layer, output_layer)
         self._loss_layer = make_loss_layer(loss, label_type, _as_cfg, **kwargs)
         # fused route state
-        self.numerics = os.environ.get('DCLR_NUMERICS', 'fp32')   # 'fp32' | 'fp16' | 'bf16' (include/deepclr_b200.h)
+        # numerics of the fused route: 'fp16' (default) | 'bf16' = tcgen05 tensor cores, 16-bit operands, fp32 accumulation;
+        # 'fp32' = SIMT fp32 everywhere.  Why fp16 is the default: its 11-bit significand is TF32's, which is what the
+        # reference's own convolutions run in on any GPU since Ampere (torch.backends.cudnn.allow_tf32 defaults to True);
+        # measured pose deviation from strict fp32: reference with TF32 0.069 deg max, this fp16 mode 0.093 deg max
+        # (profiles/r2_precision_class.json).  'fp32' is the bit-faithful, ~12x slower choice.
+        self.numerics = os.environ.get('DCLR_NUMERICS', 'fp16')
         self.fps_tie_rule: Optional[str] = None    # None = deepclr_b200.get_fps_tie_rule() at call time ('reference')
         self._native: Optional[NativeModel] = None
         self._native_key = None

@@ -123,11 +123,9 @@ def _pointwise(x, w, b):
     return torch.relu_(torch.nn.functional.conv1d(x, w.reshape(w.shape[0], w.shape[1], 1), b))
 
 
-def forward(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
-    """Reference forward (deepclr.py:488-521) on the GPU: reference CUDA ops + torch fp32 dense layers.
-    x [2B,N,C] cuda -> y [B,8]."""
-    p = cfg['params']
-    sa = p['cloud_features']['params']
+def set_abstraction(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
+    """SetAbstraction.forward (deepclr.py:88-94 -> pointnet2_modules.py:19-55): x [G,N,C] -> [G,3+F,npoint]."""
+    sa = cfg['params']['cloud_features']['params']
     with torch.no_grad():
         xyz = x[:, :, :3].contiguous()                                             # deepclr.py:30-37
         feats = x[:, :, 3:].transpose(1, 2).contiguous() if x.shape[2] > 3 else None
@@ -146,9 +144,13 @@ def forward(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
                                sd[f'_cloud_layers.0._sa0.mlps.{s}.layer{layer}.conv.bias'])
                 layer += 1
             outs.append(torch.nn.functional.max_pool2d(g, kernel_size=[1, g.size(3)]).squeeze(-1))
-        feat = torch.cat([new_xyz.transpose(1, 2), torch.cat(outs, dim=1)], dim=1)     # [2B,67,M]
-        # motion embedding (deepclr.py:157-231)
-        m = p['merge']['params']
+        return torch.cat([new_xyz.transpose(1, 2), torch.cat(outs, dim=1)], dim=1)     # [G,67,M]
+
+
+def motion_embedding(sd, cfg: dict, feat: torch.Tensor) -> torch.Tensor:
+    """MotionEmbedding.forward (deepclr.py:157-246): feat [2B,3+F,n] templates first -> [B,3+C,n]; kNN = stand-in."""
+    m = cfg['params']['merge']['params']
+    with torch.no_grad():
         k, radius = int(m['k']), float(m['radius'])
         B, D, n = feat.shape[0] // 2, feat.shape[1], feat.shape[2]
         pts0 = feat[:B].transpose(1, 2).reshape(B * n, D)
@@ -165,8 +167,12 @@ def forward(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
         if radius > 0.0:
             h = h.masked_fill((torch.norm(pos_diff, dim=2) >= radius).unsqueeze(1), 0.0)
         f = h.max(dim=2).values
-        emb = torch.cat([pts0[:, :3], f], dim=1).view(B, n, -1).transpose(1, 2).contiguous()
-        # output (deepclr.py:284-294)
+        return torch.cat([pts0[:, :3], f], dim=1).view(B, n, -1).transpose(1, 2).contiguous()
+
+
+def output_head(sd, emb: torch.Tensor) -> torch.Tensor:
+    """OutputSimple.forward (deepclr.py:284-294), dual-quaternion activation (:279-281): emb [B,3+C,n] -> [B,8]."""
+    with torch.no_grad():
         h = emb
         layer = 0
         while f'_merge_layers.1.conv._sequential.{layer}._sequential.0.weight' in sd:
@@ -182,3 +188,9 @@ def forward(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
             layer += 1
         y = torch.nn.functional.linear(h, sd['_merge_layers.1.output.weight'], sd['_merge_layers.1.output.bias'])
         return torch.cat([torch.sigmoid(y[:, 0:1]), torch.tanh(y[:, 1:4]), y[:, 4:]], dim=1)
+
+
+def forward(sd, cfg: dict, x: torch.Tensor) -> torch.Tensor:
+    """Reference forward (deepclr.py:488-521) on the GPU: reference CUDA ops + torch fp32 dense layers.
+    x [2B,N,C] cuda -> y [B,8]."""
+    return output_head(sd, motion_embedding(sd, cfg, set_abstraction(sd, cfg, x)))

@@ -113,6 +113,9 @@ def test_reference_shape_tests():
     clouds = torch.rand(10, 96, cfg.input_dim).to(DEV)
     y = torch.rand(5, cfg.label_type.dim).to(DEV)
     model = build_model(cfg).to(DEV)
+    model.numerics = 'fp32'                  # compared with the composed (torch fp32) route below
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     with torch.no_grad():
         y1, loss1, _ = model(clouds, y=y)
         assert y1.shape == (5, 8) and loss1.shape == ()

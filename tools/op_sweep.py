@@ -39,7 +39,7 @@ def main():
     ap.add_argument('--sizes', default='1024,2048,4096,8192,16384,32768,65536,131072')
     ap.add_argument('--clouds', type=int, default=8)
     ap.add_argument('--iters', type=int, default=10)
-    ap.add_argument('--ops', default='fps,ball,knn,sa')
+    ap.add_argument('--ops', default='fps,ball,knn,sa,dense')
     ap.add_argument('--no-ref', action='store_true')
     args = ap.parse_args()
     from deepclr_b200 import synth
@@ -179,6 +179,81 @@ def main():
 
             except Exception as e:       # a shape the model handle does not take: reported, the sweep goes on
                 print(json.dumps({'op': 'sa_mlp_maxpool', 'N': N, 'error': str(e)[:300]}), flush=True)
+        if 'dense' in ops and 1024 <= N <= 65536:
+            try:
+                dense_stacks(N, M, B, dev, args, have_ref)
+            except Exception as e:
+                print(json.dumps({'op': 'flow_embed/pose_head', 'N': N, 'error': str(e)[:300]}), flush=True)
+
+
+def dense_stacks(N, M, B, dev, args, have_ref):
+    """The two tensor-core stacks one by one through the stage-level C entries (dclr_flow_embed_fused /
+    dclr_pose_head_fused, fp16 operands) vs the reference composition of the same stage in torch (cuDNN / cuBLAS) in
+    strict fp32 and with torch's default TF32 convolutions: B clouds = B/2 pairs, M = N/16 samples per cloud."""
+    import yaml
+    from deepclr_b200 import synth
+    from deepclr_b200.config.config import Config
+    from deepclr_b200.data.labels import LabelType
+    from deepclr_b200.models.build import ModelType, build_model
+    from oracle import ref_cuda
+    cfg = yaml.safe_load(open(os.path.join(ROOT, 'configs', 'kitti_model.yaml')))
+    cfg['params']['cloud_features']['params']['npoint'] = [M]
+    c = Config._from_dict(cfg)
+    c.label_type = LabelType.create(c.label_type)
+    c.model_type = ModelType.create(c.model_type)
+    torch.manual_seed(0)
+    model = build_model(c).eval().to(dev)
+    model.numerics = 'fp16'
+    pairs = B // 2
+    x4 = torch.from_numpy(synth.batch('kitti', pairs, 100, n=N)).to(dev)
+    k = int(cfg['params']['merge']['params']['k'])
+    with torch.no_grad():
+        feat = model.cloud_features(x4)
+        native = model._native
+        motion = native.flow_embed(feat)
+        y = native.pose_head(motion)
+
+        def stage(fn, names):
+            native.set_timing(True)
+            for _ in range(args.iters):
+                fn()
+            torch.cuda.synchronize()
+            st, calls = native.collect_timing()
+            native.set_timing(False)
+            return sum(st.get(n, 0.0) for n in names) / max(calls, 1)
+        ms_flow = stage(lambda: native.flow_embed(feat), ('flow_embed',))
+        ms_knn = stage(lambda: native.flow_embed(feat), ('knn',))
+        ms_head = stage(lambda: native.pose_head(motion), ('pose_head_conv', 'pose_tail'))
+    fl_flow = 2.0 * pairs * M * k * (131 * 128 + 128 * 128 + 128 * 256)
+    fl_head = 2.0 * pairs * M * (259 * 256 + 256 * 256 + 256 * 512 + 512 * 512 + 512 * 1024)
+    lf = {'op': 'flow_embed', 'N': N, 'samples_per_cloud': M, 'pairs': pairs, 'k': k, 'ms': ms_flow, 'knn_ms': ms_knn,
+          'TFLOPs': fl_flow / ms_flow / 1e9, 'numerics': 'fp16 operands, fp32 accumulation (tcgen05)'}
+    lh = {'op': 'pose_head', 'N': N, 'samples_per_cloud': M, 'pairs': pairs, 'ms': ms_head, 'TFLOPs': fl_head / ms_head / 1e9,
+          'numerics': 'fp16 operands, fp32 accumulation (tcgen05) + fp32 tail'}
+    if have_ref and M * pairs * k <= 4_000_000:
+        sd = model.state_dict()
+        for tf32 in (False, True):
+            torch.backends.cudnn.allow_tf32 = tf32
+            torch.backends.cuda.matmul.allow_tf32 = tf32
+            tag = 'tf32' if tf32 else 'fp32'
+            rms = timed(lambda: ref_cuda.motion_embedding(sd, cfg, feat), 3, warm=1)
+            ref_m = ref_cuda.motion_embedding(sd, cfg, feat)
+            lf[f'ref_{tag}_ms'] = rms
+            lf[f'speedup_vs_{tag}'] = rms / (ms_flow + ms_knn)
+            lf[f'max_rel_err_vs_{tag}'] = float(((motion - ref_m).abs().max() / ref_m[:, 3:].abs().max()).item())
+            rms = timed(lambda: ref_cuda.output_head(sd, ref_m), 3, warm=1)
+            ref_y = ref_cuda.output_head(sd, motion)
+            lh[f'ref_{tag}_ms'] = rms
+            lh[f'speedup_vs_{tag}'] = rms / ms_head
+            lh[f'max_abs_err_vs_{tag}'] = float((y - ref_y).abs().max().item())
+        torch.backends.cudnn.allow_tf32 = True
+        torch.backends.cuda.matmul.allow_tf32 = False
+        lf['note'] = 'reference = torch gather/cat + 3 x (Conv1d + ReLU) + mask + max (deepclr.py:201-231), kNN stand-in included in ref and in the speed-up'
+    print(json.dumps(lf), flush=True)
+    print(json.dumps(lh), flush=True)
+    del model
+    torch.cuda.empty_cache()
+
 
 if __name__ == '__main__':
     main()
