@@ -76,15 +76,22 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
 
     if (warp == 0) ptx::tmem_alloc(s_tmem, TCOLS);
-    for (int k = tid; k < CAP; k += T) {
-        if (k < N) {
-            const float4 r = __ldg(sorted + k);
-            const int oi = __float_as_int(r.w);
-            s_x[k] = r.x; s_y[k] = r.y; s_z[k] = r.z;
-            s_idx[k] = (uint16_t)(tie_ref ? fb_rank16(oi) : oi);            // tie order (fb_rank16)
+    // stage the cloud: 8 independent 16-byte loads in flight per thread (the loop was one exposed L2 round trip per record)
+    for (int k0 = tid; k0 < CAP; k0 += 8 * T) {
+        float4 r[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int k = k0 + u * T;
+            r[u] = k < N ? __ldg(sorted + k) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int k = k0 + u * T;
+            if (k >= CAP) break;
+            const int oi = __float_as_int(r[u].w);
+            s_x[k] = r[u].x; s_y[k] = r[u].y; s_z[k] = r[u].z;
+            s_idx[k] = oi < 0 ? (uint16_t)0xffffu : (uint16_t)(tie_ref ? fb_rank16(oi) : oi);   // tie order (fb_rank16)
             if (oi == 0) *s_start = k;
-        } else {
-            s_x[k] = 0.f; s_y[k] = 0.f; s_z[k] = 0.f; s_idx[k] = 0xffffu;
         }
     }
     ptx::tc_fence_before();
