@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument('--pairs', type=int, default=64, help='pairs per step: in total (strong scaling) / per GPU (weak)')
     ap.add_argument('--scaling', default='strong', choices=['strong', 'weak'],
                     help='strong (default, BASELINE.json configs[2]): --pairs pairs in total sharded over the GPUs')
-    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU (default 2)')
+    ap.add_argument('--streams', type=int, default=0, help='model replicas / streams per GPU (default 4)')
     ap.add_argument('--partial', action='store_true', help='ModelNet-shaped pairs with partial overlap (configs[3])')
     ap.add_argument('--noise', type=float, default=0.02, help='ModelNet point noise sigma (0, 0.02, 0.04: the reference ladder)')
     ap.add_argument('--points', type=int, default=16384)
@@ -287,7 +287,7 @@ def run_native(args, rank, world, local_rank):
     model, _ = build_model_and_cfg(args.kind)
     model = model.to(dev)
     model.numerics = args.numerics
-    replicas = [model] + [model.replica() for _ in range(max(2, args.streams) - 1)]
+    replicas = [model] + [model.replica() for _ in range((args.streams if args.streams > 0 else 4) - 1)]
     gen_kw = dict(partial=True, noise=args.noise) if args.kind == 'modelnet' and args.partial else \
         (dict(noise=args.noise) if args.kind == 'modelnet' else {})
     # strong scaling (BASELINE.json configs[2]): `--pairs` pairs IN TOTAL, contiguous shards of pairs
@@ -310,13 +310,14 @@ def run_native(args, rank, world, local_rank):
         return float(t.item())
 
     def measure(B, steps, warmup):
-        """Resident and end-to-end throughput of this rank's B pairs per step.  Consecutive steps alternate between two
-        model replicas on two streams (--streams 1: one): the sampling kernel occupies one SM per cloud and is latency-
-        bound, so the dense stages of the step before it fill the rest of the GPU; every step still does all of its work
-        (measured on one B200, resident pairs/s with 1 | 2 streams: 64 pairs 55.0 k | 64.1 k, 8 pairs 12.8 k | 23.6 k)."""
+        """Resident and end-to-end throughput of this rank's B pairs per step.  Consecutive steps rotate over `--streams`
+        model replicas on as many streams (default 4; 1 = no overlap): the sampling kernel occupies one SM per cloud and is
+        latency-bound, so the other steps in flight fill the rest of the GPU; every step still does all of its work.
+        Measured on one B200, resident pairs/s with 1 | 2 | 4 streams: 64 pairs per step 55.0 k | 65.3 k | 66.3 k,
+        32 pairs 37.0 k | 59.8 k | 63.5 k, 16 pairs 22.7 k | 40.0 k | 56.6 k, 8 pairs 12.8 k | 24.4 k | 40.3 k."""
         host = [h[torch.cat([torch.arange(B), args.pairs + torch.arange(B)])].contiguous().pin_memory() for h in full]
         resident = [h.to(dev) for h in host]
-        lanes = args.streams if args.streams > 0 else 2
+        lanes = args.streams if args.streams > 0 else 4
         models = replicas[:lanes]
         streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)] if lanes > 1 else [None]
         cur = torch.cuda.current_stream(dev)
@@ -368,7 +369,7 @@ def run_native(args, rank, world, local_rank):
                'd2h_bytes_per_step': pipe.d2h_bytes // steps,
                'api': 'deepclr_b200.models.HostPipeline.run_all (pinned host batches%s%s)' % (
                    ', forward replayed from CUDA graphs' if use_graph else '',
-                   ', 2 model replicas on 2 streams' if lanes > 1 else '')}
+                   f', {lanes} model replicas on {lanes} streams' if lanes > 1 else '')}
         del pipe
         return dict(B=B, ms=ms, ms_e2e=ms_e2e, e2e=e2e, clocks=clocks, launches=launches, resident=resident, host=host,
                     lanes=lanes)

@@ -125,17 +125,20 @@ class HostPipeline:
             yield self._out[o]
 
     def run_all(self, batches: Iterable[torch.Tensor]) -> List[torch.Tensor]:
-        """All poses, synchronised: the host collects batch i-1 while batch i is already queued on the device."""
+        """All poses, synchronised.  The host collects batch i - (depth - 1) while the batches after it are already queued
+        on the device (with `replicas` compute streams several forwards are in flight at once: waiting for batch i-1 before
+        queueing batch i+1 would serialise them); a pose buffer is reused only depth + 1 batches later."""
         outs: List[torch.Tensor] = []
-        prev = None
+        pending: List = []
+        lag = self.depth - 1
         for i, y in enumerate(self.run(batches)):
-            if prev is not None:
-                self._done[(i - 1) % (self.depth + 1)].synchronize()
-                outs.append(prev.clone())
-            prev = y
-        if prev is not None:
-            self.synchronize()
-            outs.append(prev.clone())
+            pending.append((i, y))
+            if len(pending) > lag:
+                j, yj = pending.pop(0)
+                self._done[j % (self.depth + 1)].synchronize()
+                outs.append(yj.clone())
+        self.synchronize()
+        outs.extend(yj.clone() for _, yj in pending)
         return outs
 
     def synchronize(self) -> None:
