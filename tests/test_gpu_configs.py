@@ -156,3 +156,19 @@ def test_sequential_mode_with_cuda_graph_equals_plain():
         plain.reset_state()
         graphed.reset_state()
         assert not graphed.has_state()
+
+
+@pytest.mark.parametrize('use_graph', [False, True])
+def test_host_pipeline_with_replicas_equals_plain(use_graph):
+    """Several model replicas on several streams (DeepCLR.replica(), HostPipeline(replicas=3)): consecutive batches
+    overlap on the device, the poses are those of the single-stream pipeline, in order."""
+    from deepclr_b200 import synth
+    from deepclr_b200.models import HostPipeline
+    g = load_golden('kitti_small_b2')
+    model, _ = build_from_golden(g, DEV)
+    batches = [torch.from_numpy(synth.batch('kitti', 2, 600 + i, n=int(g['n']))).pin_memory() for i in range(11)]
+    plain = HostPipeline(model).run_all(batches)
+    multi = HostPipeline(model, depth=6, replicas=3, use_cuda_graph=use_graph).run_all(batches)
+    assert len(plain) == len(multi) == 11
+    for a, b in zip(plain, multi):
+        assert torch.equal(a, b)
