@@ -58,6 +58,22 @@ def main():
                          'duration_ms_under_ncu': float(d['gpu__time_duration.sum'].replace(',', '')) * dur_unit}
     if traffic:
         json.dump(traffic, open(os.path.join(dst, f'{tag}_ncu_traffic.json'), 'w'), indent=1)
+    # source-level view of the sampling kernel: address, samples, executions, dominant stall, SASS
+    rep = os.path.join(src, 'full_fps_tmem_kernel.ncu-rep')
+    if os.path.exists(rep):
+        out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
+        rows = list(csv.reader(out.splitlines()))
+        if len(rows) > 2:
+            hdr = rows[1]
+            ci = {h: i for i, h in enumerate(hdr)}
+            stalls = [h for h in hdr if h.startswith('stall_') and 'Not Issued' not in h]
+            with open(os.path.join(dst, f'{tag}_ncu_fps_tmem_kernel_source.csv'), 'w', newline='') as f:
+                w = csv.writer(f)
+                w.writerow(['address', 'samples', 'instructions_executed', 'top_stall', 'sass'])
+                for r in rows[2:]:
+                    n = int(r[ci['# Samples']] or 0)
+                    top = max(stalls, key=lambda h: int(r[ci[h]] or 0)) if n else ''
+                    w.writerow([r[ci['Address']][-5:], n, r[ci['Instructions Executed']], top[6:], r[ci['Source']]])
     lp = os.path.join(src, 'launches.csv')
     if os.path.exists(lp):
         lines = [l for l in open(lp) if l.startswith('"')]
