@@ -336,7 +336,10 @@ int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, in
     const char *env_shape = getenv("DCLR_FPS_SHAPE"), *env_mp = getenv("DCLR_FPS_MP");
     const int shape = env_shape ? atoi(env_shape) : 8;
     const int mp = env_mp ? atoi(env_mp) : 3;      // measured per 128 clouds: 1 0.567 | 2 0.457 | 3 0.428 | 4 0.435 | 6 0.490 ms
-    if (mp >= 1) rc = fps_tmem_launch(sorted, B, N, npoint, tie_ref, shape, mp, idx, nx, st);
+    const char *env_cl = getenv("DCLR_FPS_CLUSTER");        // 1: one cloud over a cluster of two CTAs (fps_cluster.cu)
+    const int use_cluster = env_cl ? atoi(env_cl) : 0;
+    if (mp >= 1 && use_cluster && N > 8192) rc = fps_cluster_launch(sorted, B, N, npoint, tie_ref, mp, idx, nx, st);
+    else if (mp >= 1) rc = fps_tmem_launch(sorted, B, N, npoint, tie_ref, shape, mp, idx, nx, st);
     else if (N <= 4096) rc = launch_bucket_any<2>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);
     else if (N <= 8192) rc = launch_bucket_any<4>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);
     else rc = launch_bucket_any<8>(shape, sorted, B, N, npoint, tie_ref, idx, nx, st);

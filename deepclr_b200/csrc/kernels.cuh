@@ -19,6 +19,9 @@ int fps_bucket_l2_launch(const float4 *sorted, float *tmin, int B, int N, int np
 // fps_tmem.cu: running minima in tensor memory, up to mp samples per round; sorted = fps_sort_kernel's records, N <= 16384
 int fps_tmem_launch(const float4 *sorted, int B, int N, int npoint, int tie_ref, int nw, int mp, int32_t *idx, float *nx,
                     cudaStream_t st);
+// fps_cluster.cu: the same, one cloud split over a cluster of two CTAs (8192 < N <= 16384)
+int fps_cluster_launch(const float4 *sorted, int B, int N, int npoint, int tie_ref, int mp, int32_t *idx, float *nx,
+                       cudaStream_t st);
 // after_sort (optional) is recorded on st between the sort and the sampling kernel
 int fps_bucket_launch(const float *pts, int stride, int B, int N, int npoint, int tie_rule, int32_t *idx, float *new_xyz,
                       void *ws, cudaStream_t st, int *used, cudaEvent_t after_sort = nullptr);

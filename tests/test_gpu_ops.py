@@ -242,7 +242,8 @@ def test_device_to_matrix_and_kitti_errors_match_host(lt_name):
     np.testing.assert_allclose(trans.cpu().numpy(), ref[:, 1], atol=1e-12)
 
 
-@pytest.mark.parametrize('shape,mp', [(8, 0), (16, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 1), (16, 2), (16, 4), (32, 0)])
+@pytest.mark.parametrize('shape,mp', [(8, 0), (16, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 1), (16, 2), (16, 4), (32, 0),
+                                      (-2, 2), (-2, 3), (-2, 4), (-2, 6)])
 def test_fps_multipick_variants_are_exact(p2, shape, mp, monkeypatch):
     """Every warps-per-cloud x samples-per-round variant of the bucketed kernels (fps_tmem.cu: minima in tensor memory,
     mp >= 1 samples per round; fps_bucket.cu: mp = 0, registers; DCLR_FPS_SHAPE / DCLR_FPS_MP are read per call) returns the indices of the serial algorithm (sampling_gpu.cu:113-208), under both tie
@@ -250,8 +251,9 @@ def test_fps_multipick_variants_are_exact(p2, shape, mp, monkeypatch):
     ragged N, and npoint > N (all minima reach 0: the strict-> start of the reference, sampling_gpu.cu:119-137)."""
     import deepclr_b200
     from deepclr_b200 import synth
-    monkeypatch.setenv('DCLR_FPS_SHAPE', str(shape))
+    monkeypatch.setenv('DCLR_FPS_SHAPE', str(abs(shape) if shape > 0 else 8))
     monkeypatch.setenv('DCLR_FPS_MP', str(mp))
+    monkeypatch.setenv('DCLR_FPS_CLUSTER', '1' if shape < 0 else '0')       # shape -2: a cluster of two CTAs per cloud (fps_cluster.cu)
     rng = np.random.default_rng(7)
     dup = rng.uniform(-40, 40, (2, 16384, 3)).astype(np.float32)
     dup[:, rng.permutation(16384)[:5000]] = dup[:, rng.integers(0, 16384, 5000)]

@@ -14,8 +14,8 @@ from deepclr_b200 import _lib, synth  # noqa: E402
 
 pool = np.stack([synth.kitti_pair(1234 + i, 16384)[i % 2] for i in range(16)])
 variants = [(8, 0), (8, 1), (8, 2), (8, 3), (8, 4), (8, 6), (16, 2), (16, 4)]
-if len(sys.argv) > 1:
-    variants = [tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]]
+if len(sys.argv) > 1:         # e.g. 8x3 (warps x samples per round), c3 = cluster of two CTAs per cloud, 3 samples per round
+    variants = [(-2, int(a[1:])) if a[0] == 'c' else tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]]
 ref = None
 for G in (128, 32, 16, 2):
     x = torch.from_numpy(np.ascontiguousarray(pool[np.arange(G) % 16])).cuda()
@@ -24,7 +24,8 @@ for G in (128, 32, 16, 2):
     nx = torch.empty((G, 1024, 3), dtype=torch.float32, device='cuda')
     base = None
     for shape, mp in variants:
-        os.environ['DCLR_FPS_SHAPE'], os.environ['DCLR_FPS_MP'] = str(shape), str(mp)
+        os.environ['DCLR_FPS_SHAPE'], os.environ['DCLR_FPS_MP'] = str(shape if shape > 0 else 8), str(mp)
+        os.environ['DCLR_FPS_CLUSTER'] = '1' if shape < 0 else '0' 
         call = lambda: _lib.check(_lib.lib().dclr_fps(_lib.ptr(x), 4, G, 16384, 1024, 1, _lib.ptr(idx), _lib.ptr(nx),
                                                       _lib.stream_ptr()), 'fps')
         for _ in range(3):
