@@ -322,18 +322,21 @@ __global__ void __launch_bounds__(KNNF_WARPS * 32)
 knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
                 int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local,
                 float4 *__restrict__ nbr4) {
-    __shared__ float s_x[KPL * 32], s_y[KPL * 32], s_z[KPL * 32];
+    __shared__ __align__(8) float s_x[KPL * 32], s_y[KPL * 32], s_z[KPL * 32];
     __shared__ uint64_t s_cand[KNNF_WARPS][KNNF_CAP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.y;
     const float *xb = x + (size_t)b * Nx * 3;
+    // candidates that do not exist sit far away (d = 3e36: finite, never among the k <= Nx nearest) -- no bounds test in
+    // the distance loop
     for (int j = tid; j < KPL * 32; j += KNNF_WARPS * 32) {
         const bool ok = j < Nx;
-        s_x[j] = ok ? __ldg(xb + j * 3) : 0.f;
-        s_y[j] = ok ? __ldg(xb + j * 3 + 1) : 0.f;
-        s_z[j] = ok ? __ldg(xb + j * 3 + 2) : 0.f;
+        s_x[j] = ok ? __ldg(xb + j * 3) : 1e18f;
+        s_y[j] = ok ? __ldg(xb + j * 3 + 1) : 1e18f;
+        s_z[j] = ok ? __ldg(xb + j * 3 + 2) : 1e18f;
     }
     __syncthreads();
+    static_assert(KPL % 2 == 0, "candidate pairs");
     const uint64_t KMAX = ~0ull;
     const unsigned lt_mask = (1u << lane) - 1u;
     for (int qi = 0; qi < KNNF_QPW; ++qi) {
@@ -341,15 +344,28 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
         if (q >= Ny) break;                                     // warp-uniform
         const size_t gy = (size_t)b * Ny + q;
         const float qx = __ldg(y + gy * 3), qy = __ldg(y + gy * 3 + 1), qz = __ldg(y + gy * 3 + 2);
+        // d[2 i], d[2 i + 1] = candidates 2 (i * 32 + lane), + 1: two per packed instruction, each half rounded exactly like
+        // the scalar expression.  torch-cluster: tmp_dist += (x - y)^2 per dimension, x = candidate, y = query
         float d[KPL];
         float lmin = INFINITY;
+        {
+            uint64_t qxp, qyp, qzp;
+            asm("mov.b64 %0, {%1, %1};" : "=l"(qxp) : "f"(qx));
+            asm("mov.b64 %0, {%1, %1};" : "=l"(qyp) : "f"(qy));
+            asm("mov.b64 %0, {%1, %1};" : "=l"(qzp) : "f"(qz));
 #pragma unroll
-        for (int i = 0; i < KPL; ++i) {
-            const int j = i * 32 + lane;
-            // torch-cluster: tmp_dist += (x - y)^2 per dimension, x = candidate, y = query
-            const float v = sqdist_tc(s_x[j] - qx, s_y[j] - qy, s_z[j] - qz);
-            d[i] = j < Nx ? v : INFINITY;
-            lmin = fminf(lmin, d[i]);
+            for (int i = 0; i < KPL / 2; ++i) {
+                const int j = 2 * (i * 32 + lane);            // one 8-byte shared load per coordinate and candidate pair
+                uint64_t dx, dy, dz, acc;
+                asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dx) : "l"(*reinterpret_cast<const uint64_t *>(s_x + j)), "l"(qxp));
+                asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dy) : "l"(*reinterpret_cast<const uint64_t *>(s_y + j)), "l"(qyp));
+                asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dz) : "l"(*reinterpret_cast<const uint64_t *>(s_z + j)), "l"(qzp));
+                asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(acc) : "l"(dx));
+                asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(acc) : "l"(dy), "l"(acc));
+                asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(acc) : "l"(dz), "l"(acc));
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(d[2 * i]), "=f"(d[2 * i + 1]) : "l"(acc));
+                asm("min.f32 %0, %0, %1, %2;" : "+f"(lmin) : "f"(d[2 * i]), "f"(d[2 * i + 1]));
+            }
         }
         // threshold: k rounds of "take the smallest remaining lane minimum" (d >= 0, so its bit image is ordered)
         uint32_t v = __float_as_uint(lmin), T = 0;
@@ -377,7 +393,7 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
 #pragma unroll
             for (int i = 0; i < KPL; ++i)
                 if (__float_as_uint(d[i]) <= T)
-                    cand[off++] = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(i * 32 + lane);
+                    cand[off++] = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(2 * ((i >> 1) * 32 + lane) + (i & 1));
             __syncwarp();
             c0 = lane < total ? cand[lane] : KMAX;
             c1 = lane + 32 < total ? cand[lane + 32] : KMAX;
@@ -424,7 +440,7 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
                 lm = KMAX;
 #pragma unroll
                 for (int i = 0; i < KPL; ++i) {
-                    const uint64_t key = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(i * 32 + lane);
+                    const uint64_t key = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(2 * ((i >> 1) * 32 + lane) + (i & 1));
                     lm = (d[i] != INFINITY && key < lm) ? key : lm;
                 }
             }
@@ -436,7 +452,7 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
                 } else {
 #pragma unroll
                     for (int i = 0; i < KPL; ++i)
-                        if ((uint32_t)win == (uint32_t)(i * 32 + lane)) d[i] = INFINITY;
+                        if ((uint32_t)win == (uint32_t)(2 * ((i >> 1) * 32 + lane) + (i & 1))) d[i] = INFINITY;
                 }
             }
             if (lane == 0) {
