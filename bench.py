@@ -540,9 +540,11 @@ def run_native(args, rank, world, local_rank):
                                   sms_occupied=min(G, 148), sm_count=148, hbm_frac=roof_stages['fps']['frac'],
                                   note='dependent sampling rounds (up to 3 exact samples per round); HBM bytes are read once')
     if 'ball_query' in roof_stages:
-        roof_stages['ball_query'].update(note='dense-equivalent bytes (the reference writes fully padded index tensors); the '
+        # the fused path writes only genuine hits: no fraction of the HBM peak is claimed for bytes it does not move
+        roof_stages['ball_query'].update(dense_equiv_frac=roof_stages['ball_query']['frac'], frac=None, bound='issue / L2 latency',
+                                         note='dense-equivalent bytes (the reference writes fully padded index tensors); the '
                                               'fused path writes only genuine hits')
-    top = max((k for k in per_call if k in roof_stages), key=per_call.get)
+    top = max((k for k in per_call if k in roof_stages and per_call[k] > 0), key=per_call.get)
     roof = dict(roof_stages[top])
     roof.update({'kernel': STAGE_KERNEL.get(top, top), 'stage': top, 'traffic': ncu_traffic(top, args), 'peak_source': peaks['src'],
                  'ms_per_launch': per_call[top], 'share_of_step': per_call[top] / sum(per_call.values())})
