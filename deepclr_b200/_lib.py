@@ -27,6 +27,8 @@ _SIGNATURES = {
     'dclr_version': (ctypes.c_char_p, []),
     'dclr_last_error': (ctypes.c_char_p, []),
     'dclr_fps': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    'dclr_fps_static': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    'dclr_fps_static_limits': (c_int, [c_void_p, c_void_p]),
     'dclr_gather': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'dclr_pose_to_matrix': (c_int, [c_void_p, c_int, c_int, ctypes.c_float, c_void_p, c_void_p]),
     'dclr_pose_errors': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),

@@ -56,6 +56,21 @@ const char *dclr_last_error(void);
 int dclr_fps(const float *pts, int pt_stride, int B, int N, int npoint, int tie_rule, int32_t *idx_out,
              float *new_xyz_out, void *stream);
 
+/*
+ * dclr_fps without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Arguments, kernels and results are those of dclr_fps; the scratch dclr_fps takes from the stream-ordered pool (the
+ * Z-ordered records of the bucketed kernels, 16 bytes per point) is a file-scope device array of the library
+ * (csrc/fps_static.cu, 2 MiB, held by every GPU that loads the library until the process exits).  Limits, reported by
+ * dclr_fps_static_limits: N <= 16384 points per cloud and B * N <= 131072 points per call; anything larger returns
+ * DCLR_E_INVALID with a message naming the limit.  The call makes no cudaMalloc / cudaFree / pool allocation.
+ * Every call shares the one array: calls that overlap on the GPU (different streams, or several host threads without
+ * ordering) race on it; calls on one stream are ordered and safe.  Nothing in it has to be cleared between calls.
+ */
+int dclr_fps_static(const float *pts, int pt_stride, int B, int N, int npoint, int tie_rule, int32_t *idx_out,
+                    float *new_xyz_out, void *stream);
+int dclr_fps_static_limits(int *max_points_per_cloud, int *max_points_per_call);
+
 /* out[b,c,j] = feat[b,c,idx[b,j]].  Replaces pointnet2_cuda.gather_points_wrapper (sampling.cpp:11-20). */
 int dclr_gather(const float *feat, const int32_t *idx, int B, int C, int N, int M, float *out, void *stream);
 
