@@ -647,21 +647,34 @@ constexpr int HEAD_LAYERS = 5;
 // Weight ring shape (overridable for tools/ab.sh).  Every tile costs an exposed mbarrier wait + commit (~115 cycles,
 // tools/micro/mma_ring.cu), so tiles are as wide as the shared-memory budget allows: measured head time per 64 pairs
 // 64 x 5 stages 0.184 ms | 80 x 4 0.174 | 96 x 3 0.168 | 96 x 2 0.192 | 128 x 2 0.177 | **112 x 3 0.163**.
+// With two issuing warps (below) stage s belongs to warp s % 2 (tile `it` of the stream sits in stage it % STAGES and
+// belongs to warp it % 2, so STAGES must be even): a consumer then never waits on a stage whose previous occupant was
+// another warp's, and the 1-bit phase parity of its mbarrier cannot alias.  4 x 20 KB.
 #ifndef DCLR_HEAD_KT
-#define DCLR_HEAD_KT 112
-#define DCLR_HEAD_STAGES 3
+#define DCLR_HEAD_KT 80
+#define DCLR_HEAD_STAGES 4
 #endif
 constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 112 = 28 KB)
 constexpr int HEAD_STAGES = DCLR_HEAD_STAGES;
 constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
 constexpr int HEAD_EPI_WARPS = 8;                // 4 TMEM lane quarters x 2 column halves
-constexpr int HEAD_PROD_WARP = HEAD_EPI_WARPS, HEAD_MMA_WARP = HEAD_EPI_WARPS + 1;
-constexpr int HEAD_THREADS = (HEAD_EPI_WARPS + 2) * 32;
+// TWO MMA-issuing warps: the issuing warp is bound by its own instruction latencies (~15 dependent scalar instructions per
+// tcgen05.mma plus ~100 per weight tile: 85-100 cycles per 64-cycle MMA with one warp, tools/head_trace.py), not by the
+// tensor pipe or the weight stream (copies disabled: same timeline).  Two warps with their own accumulator blocks keep
+// the pipe fed (tools/micro/mma_dual.cu): warp q takes the output blocks nc = 2p + q of every layer, the weight tiles of
+// a block pair are streamed interleaved (pair p: k-tile 0 of block 2p, k-tile 0 of block 2p+1, k-tile 1 of ...).
+constexpr int HEAD_MMA_WARPS = 2;
+// One producer lane per issuing warp: a lane needs ~345 cycles per cp.async.bulk whatever its size (wait + expect_tx +
+// issue, tools/micro/tma_stream.cu), i.e. 59 B/cycle with 20 KB tiles against the 64 B/cycle the tensor pipe consumes.
+constexpr int HEAD_PROD_WARP = HEAD_EPI_WARPS, HEAD_MMA_WARP = HEAD_EPI_WARPS + HEAD_MMA_WARPS;
+constexpr int HEAD_THREADS = (HEAD_EPI_WARPS + 2 * HEAD_MMA_WARPS) * 32;
+constexpr int HEAD_FIN_BUFS = 2 * HEAD_MMA_WARPS;    // last layer: TMEM blocks in flight, two per issuing warp
+static_assert(HEAD_STAGES % HEAD_MMA_WARPS == 0 && HEAD_KT % 16 == 0, "weight ring: a stage has one consuming warp");
 
 struct HeadArgs {
     const uint16_t *feat;   // [B*n, C0] motion features, 16-bit operand format
     const float *xyz;       // [B*n, 3] template sample coordinates
-    const uint16_t *w;      // packed weight tiles in (layer, 128-row block, K block) order
+    const uint16_t *w;      // packed weight tiles in (layer, pair of 128-row blocks, K block, block of the pair) order
     const float *bias;      // biases of the 5 layers, concatenated
     float *pooled;          // [B, out[4]] zero-initialised; max over the points
     int B, n, C0;
@@ -682,14 +695,14 @@ head_tc_kernel(HeadArgs a) {
     float *s_bias = reinterpret_cast<float *>(s_wt + HEAD_STAGES * HEAD_TILE_BYTES);
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_bias + nbias);
     uint64_t *full = s_bar, *empty = s_bar + HEAD_STAGES, *act_ready = empty + HEAD_STAGES,
-             *layer_done = act_ready + 1, *fin_done = layer_done + 1, *fin_free = fin_done + 2;
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(fin_free + 2);
+             *layer_done = act_ready + 1, *fin_done = layer_done + 1, *fin_free = fin_done + HEAD_FIN_BUFS;
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(fin_free + HEAD_FIN_BUFS);
 
     if (tid == 0) {
         for (int i = 0; i < HEAD_STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
         ptx::mbar_init(act_ready, HEAD_EPI_WARPS * 32);
-        ptx::mbar_init(layer_done, 1);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&fin_done[i], 1); ptx::mbar_init(&fin_free[i], HEAD_EPI_WARPS * 32); }
+        ptx::mbar_init(layer_done, HEAD_MMA_WARPS);
+        for (int i = 0; i < HEAD_FIN_BUFS; ++i) { ptx::mbar_init(&fin_done[i], 1); ptx::mbar_init(&fin_free[i], HEAD_EPI_WARPS * 32); }
         ptx::fence_mbar_init();
     }
     if (warp == HEAD_MMA_WARP) ptx::tmem_alloc(s_tmem, 512);
@@ -700,72 +713,104 @@ head_tc_kernel(HeadArgs a) {
     const uint32_t tmem_base = *s_tmem;
     constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
 
-    if (warp == HEAD_PROD_WARP) {
-        // ===================== weight producer: stream every tile of every layer, once per row tile ============
+    if (warp >= HEAD_PROD_WARP && warp < HEAD_MMA_WARP) {
+        // ===================== weight producers: stream every tile of every layer, once per row tile ===========
+        // producer `pq` feeds issuing warp `pq` (the tiles with it % HEAD_MMA_WARPS == pq, in that warp's stages)
+        const int pq = warp - HEAD_PROD_WARP;
         if (lane == 0) {
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
                 const uint8_t *src = reinterpret_cast<const uint8_t *>(a.w);
-                for (int l = 0; l < HEAD_LAYERS; ++l)
-                    for (int nc = 0; nc < a.out[l] / 128; ++nc)
-                        for (int k0 = 0; k0 < a.Kp[l]; k0 += HEAD_KT, ++it) {
+                for (int l = 0; l < HEAD_LAYERS; ++l) {
+                    const int nblocks = a.out[l] / 128;
+                    for (int p0 = 0; p0 < nblocks; p0 += HEAD_MMA_WARPS)
+                        for (int k0 = 0; k0 < a.Kp[l]; k0 += HEAD_KT)
+                            for (int q = 0; q < HEAD_MMA_WARPS; ++q, ++it) {
                             const uint32_t bytes = 128u * min(HEAD_KT, a.Kp[l] - k0) * 2;
+                            if (q != pq) {
+                                if (p0 + q < nblocks) src += bytes;
+                                continue;
+                            }
                             const int st = it % HEAD_STAGES;
                             ptx::mbar_wait(&empty[st], ((it / HEAD_STAGES) & 1) ^ 1);
+                            if (p0 + q >= nblocks) {       // odd number of blocks: an empty slot keeps the stage <-> warp map
+                                ptx::mbar_arrive(&full[st]);
+                                continue;
+                            }
+#ifdef DCLR_HEAD_NOCOPY       // timing experiment only (tools/head_trace.py): the weights "arrive" at once
+                            ptx::mbar_arrive(&full[st]);
+#else
                             ptx::mbar_expect_tx(&full[st], bytes);
                             ptx::bulk_g2s(s_wt + st * HEAD_TILE_BYTES, src, bytes, &full[st]);
+#endif
                             src += bytes;
                         }
+                }
             }
         }
-    } else if (warp == HEAD_MMA_WARP) {
-        // ===================== MMA issuer: the whole warp runs the loop, one elected lane issues ================
+    } else if (warp >= HEAD_MMA_WARP) {
+        // ===================== MMA issuers: each warp runs the loop converged, one elected lane issues ==========
+        // Warp q owns the output blocks nc = 2p + q (and, in the last layer, the TMEM buffer q); `it` counts the weight
+        // tiles of the stream, both warps count all of them and take their own.
         {
+            const int q = warp - HEAD_MMA_WARP;
             const uint32_t act_lo = sdesc_lo(ptx::smem_u32(s_act)), wt_lo = sdesc_lo(ptx::smem_u32(s_wt));
-            uint32_t st = 0, ph = 0, n_ready = 0, fin_use[2] = {0, 0};
+            uint32_t it = 0, n_ready = 0, fin_use[2] = {0, 0};
             for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
                     ptx::tc_fence_after();
-                    if (lane == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
+                    if (lane == 0 && q == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
                     const bool last = l == HEAD_LAYERS - 1;
                     const int Kp = a.Kp[l], nblocks = a.out[l] / 128;
-                    for (int nc = 0; nc < nblocks; ++nc) {
-                        uint32_t dcol = tmem_base + nc * 128;
-                        if (last) {
-                            const int buf = nc & 1;
-                            if (fin_use[buf] > 0) {
-                                ptx::mbar_wait(&fin_free[buf], (fin_use[buf] - 1) & 1);
+                    const int ktiles = (Kp + HEAD_KT - 1) / HEAD_KT;
+                    for (int p0 = 0; p0 < nblocks; p0 += HEAD_MMA_WARPS) {
+                        const int nc = p0 + q;
+                        if (nc >= nblocks) {                           // empty slots of an odd block count: pass them on
+                            uint32_t mine = it + q;
+                            for (int k0 = 0; k0 < Kp; k0 += HEAD_KT, mine += HEAD_MMA_WARPS) {
+                                const uint32_t st = mine % HEAD_STAGES;
+                                ptx::mbar_wait(&full[st], (mine / HEAD_STAGES) & 1);
+                                ptx::mma_commit_warp(&empty[st]);
+                            }
+                        } else {
+                            uint32_t dcol = tmem_base + nc * 128;
+                            const int buf = nc % HEAD_FIN_BUFS, bj = (nc / HEAD_MMA_WARPS) & 1;   // my two buffers alternate
+                            if (last) {
+                                if (fin_use[bj] > 0) {
+                                    ptx::mbar_wait(&fin_free[buf], (fin_use[bj] - 1) & 1);
+                                    ptx::tc_fence_after();
+                                }
+                                ++fin_use[bj];
+                                dcol = tmem_base + buf * 128;
+                            }
+                            uint32_t a_lo = act_lo, acc = 0, mine = it + q;
+                            for (int k0 = 0; k0 < Kp; k0 += HEAD_KT, mine += HEAD_MMA_WARPS) {
+                                const uint32_t st = mine % HEAD_STAGES, ph = (mine / HEAD_STAGES) & 1;
+                                ptx::mbar_wait(&full[st], ph);
                                 ptx::tc_fence_after();
-                            }
-                            ++fin_use[buf];
-                            dcol = tmem_base + buf * 128;
-                        }
-                        uint32_t a_lo = act_lo, acc = 0;
-                        for (int k0 = 0; k0 < Kp; k0 += HEAD_KT) {
-                            ptx::mbar_wait(&full[st], ph);
-                            ptx::tc_fence_after();
-                            const uint32_t w_lo = wt_lo + st * (HEAD_TILE_BYTES >> 4);
-                            // hidden layers: D = X.W^T (A = activations); last layer transposed (A = weights)
-                            const uint32_t p_lo = last ? w_lo : a_lo, q_lo = last ? a_lo : w_lo;
-                            if (Kp - k0 >= HEAD_KT) {                       // full K tile: HEAD_KT / 16 MMAs, unrolled
-                                ptx::mma_f16_ss_warp(dcol, sdesc(p_lo), sdesc(q_lo), IDESC, acc);
+                                const uint32_t w_lo = wt_lo + st * (HEAD_TILE_BYTES >> 4);
+                                // hidden layers: D = X.W^T (A = activations); last layer transposed (A = weights)
+                                const uint32_t p_lo = last ? w_lo : a_lo, q_lo = last ? a_lo : w_lo;
+                                if (Kp - k0 >= HEAD_KT) {                   // full K tile: HEAD_KT / 16 MMAs, unrolled
+                                    ptx::mma_f16_ss_warp(dcol, sdesc(p_lo), sdesc(q_lo), IDESC, acc);
 #pragma unroll
-                                for (int ks = 1; ks < HEAD_KT / 16; ++ks)
-                                    ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, 1u);
-                            } else {
-                                for (int ks = 0; ks < (Kp - k0) / 16; ++ks)
-                                    ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, ks ? 1u : acc);
+                                    for (int ks = 1; ks < HEAD_KT / 16; ++ks)
+                                        ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, 1u);
+                                } else {
+                                    for (int ks = 0; ks < (Kp - k0) / 16; ++ks)
+                                        ptx::mma_f16_ss_warp(dcol, sdesc(p_lo + ks * SDESC_KSTEP), sdesc(q_lo + ks * SDESC_KSTEP), IDESC, ks ? 1u : acc);
+                                }
+                                acc = 1;
+                                a_lo += (HEAD_KT / 16) * SDESC_KSTEP;
+                                ptx::mma_commit_warp(&empty[st]);      // frees the weight stage when the MMAs retire
                             }
-                            acc = 1;
-                            a_lo += (HEAD_KT / 16) * SDESC_KSTEP;
-                            ptx::mma_commit_warp(&empty[st]);          // frees the weight stage when the MMAs retire
-                            if (++st == HEAD_STAGES) { st = 0; ph ^= 1; }
+                            if (last) ptx::mma_commit_warp(&fin_done[buf]);
                         }
-                        if (last) ptx::mma_commit_warp(&fin_done[nc & 1]);
+                        it += ktiles * HEAD_MMA_WARPS;
                     }
-                    if (!last) ptx::mma_commit_warp(layer_done);
-                    if (lane == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
+                    if (!last) ptx::mma_commit_warp(layer_done);       // one arrival per issuing warp
+                    if (lane == 0 && q == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
                 }
             }
         }
@@ -776,7 +821,7 @@ head_tc_kernel(HeadArgs a) {
         const int r = q * 32 + lane;
         const uint32_t act_row = ptx::smem_u32(s_act) + r * 16;
         const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
-        uint32_t n_done = 0, fin_cnt[2] = {0, 0};
+        uint32_t n_done = 0, fin_par = 0;            // bit b: phase parity of fin_done[b]
         const int C0 = a.C0, n = a.n;
         const int cc = C0 / 8, cmid = cc / 2, kc0 = a.Kp[0] / 8;
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
@@ -829,8 +874,8 @@ head_tc_kernel(HeadArgs a) {
             //      The halves split the 128 columns; both contribute through atomicMax.
             const int nvalid = min(128, n - p0);
             for (int nc = 0; nc < a.out[HEAD_LAYERS - 1] / 128; ++nc) {
-                const int buf = nc & 1;
-                ptx::mbar_wait(&fin_done[buf], fin_cnt[buf] & 1); ++fin_cnt[buf];
+                const int buf = nc % HEAD_FIN_BUFS;
+                ptx::mbar_wait(&fin_done[buf], (fin_par >> buf) & 1); fin_par ^= 1u << buf;
                 ptx::tc_fence_after();
                 if (tid == 0) TRACE(tr0 + 10 + nc);
                 float cur = -INFINITY;
@@ -956,7 +1001,7 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
                    (size_t)FLOW_SLOTS * 128 * t->K0p * 2 + (256 + H3) * 4 + 2 * FLOW_SLOTS * 4 * 4 +
                    (1 + 5 * FLOW_SLOTS) * 8 + 16 + FLOW_SLOTS * 128 * 16 + FLOW_SLOTS * FLOW_PROD * FLOW_STAGE_BYTES;
 
-    // ---- head: tiles in (layer, 128-row block, 64-wide K block) order
+    // ---- head: tiles in (layer, pair of 128-row blocks, K block, block of the pair) order: head_tc_kernel's stream
     size_t head_elems = 0;
     int nbias = 0;
     t->head_act_k = 0;
@@ -976,19 +1021,20 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     int boff = 0;
     for (int l = 0; l < HEAD_LAYERS; ++l) {
         const TcLayerSpec &s = sp[3 + l];
-        for (int nc = 0; nc < s.out / 128; ++nc)
-            for (int k0 = 0; k0 < t->head_Kp[l]; k0 += HEAD_KT) {
-                const int kt = t->head_Kp[l] - k0 < HEAD_KT ? t->head_Kp[l] - k0 : HEAD_KT;
-                if ((rc = pack_any(fmt, s.W, l < HEAD_LAYERS - 1 ? s.b : nullptr, l == 0 ? H3 + 9 : s.in, s.out, s.in,
-                                   l == 0 ? H3 : 0, nc * 128, 128, k0, kt, p)))
-                    return bail(rc);
-                p += (size_t)128 * kt;
-            }
+        for (int p0 = 0; p0 < s.out / 128; p0 += HEAD_MMA_WARPS)
+            for (int k0 = 0; k0 < t->head_Kp[l]; k0 += HEAD_KT)
+                for (int nc = p0; nc < std::min(p0 + HEAD_MMA_WARPS, s.out / 128); ++nc) {
+                    const int kt = t->head_Kp[l] - k0 < HEAD_KT ? t->head_Kp[l] - k0 : HEAD_KT;
+                    if ((rc = pack_any(fmt, s.W, l < HEAD_LAYERS - 1 ? s.b : nullptr, l == 0 ? H3 + 9 : s.in, s.out, s.in,
+                                       l == 0 ? H3 : 0, nc * 128, 128, k0, kt, p)))
+                        return bail(rc);
+                    p += (size_t)128 * kt;
+                }
         TC_CUDA(cudaMemcpy(t->head_b + boff, s.b, s.out * 4, cudaMemcpyDeviceToDevice));
         boff += s.out;
     }
     t->head_smem = (size_t)128 * t->head_act_k * 2 + HEAD_STAGES * HEAD_TILE_BYTES + (size_t)nbias * 4 +
-                   (2 * HEAD_STAGES + 6) * 8 + 16;
+                   (2 * HEAD_STAGES + 2 + 2 * HEAD_FIN_BUFS) * 8 + 16;
     TC_CUDA(cudaDeviceSynchronize());
     if (t->flow_smem > 232448 || t->head_smem > 232448)
         return bail(fail(DCLR_E_UNSUPPORTED, "tensor-core path: shared memory budget exceeded (%zu / %zu bytes)",

@@ -31,7 +31,54 @@ __global__ void __launch_bounds__(96, 1) k(long long *out, int tiles, int mode) 
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tb = s_tmem;
-    if (warp == 0 && (mode & 128)) {
+    if (warp == 0 && (mode & 256)) {
+        // converged warp, bookkeeping tucked under the tile's own MMAs: after the first J MMAs of tile t, commit tile
+        // t-1's stage (the commit also covers those J MMAs: harmless, the stage is released ~J x 64 cycles later) and
+        // wait for tile t+1's stage; then the remaining MMAs.  J = mode >> 9.
+        const int J = mode >> 9;
+        const uint32_t a0 = ptx::smem_u32(smem), b0 = a0 + 16384;
+        constexpr uint32_t ID = make_idesc(128, 128);
+        uint32_t st = 0, ph = 0;
+        auto mma = [&](uint32_t d, int ks) {
+            const uint64_t ad = make_sdesc(a0 + (ks & 3) * 4096, 2048), bd = make_sdesc(b0 + (ks & 3) * 4096, 2048);
+            asm volatile(
+                "{\n\t.reg .pred p, e;\n\t"
+                "elect.sync _|e, 0xffffffff;\n\t"
+                "setp.ne.b32 p, %4, 0;\n\t"
+                "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(ad), "l"(bd), "r"(ID), "r"(1u) : "memory");
+        };
+        long long t0 = clock64();
+        ptx::mbar_wait(&full[0], 0);
+        ptx::tc_fence_after();
+        for (int t = 0; t < tiles; ++t) {
+            const uint32_t d = tb + (t & 3) * 128;
+            uint32_t nst = st + 1, nph = ph;
+            if (nst == STAGES) { nst = 0; nph ^= 1; }
+#pragma unroll
+            for (int ks = 0; ks < MMAS; ++ks) {
+                if (ks == J) {
+                    if (t > 0) {
+                        const uint32_t pst = st == 0 ? STAGES - 1 : st - 1;
+                        asm volatile(
+                            "{\n\t.reg .pred e;\n\t"
+                            "elect.sync _|e, 0xffffffff;\n\t"
+                            "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(ptx::smem_u32(&empty[pst])) : "memory");
+                    }
+                    if (t + 1 < tiles) { ptx::mbar_wait(&full[nst], nph); ptx::tc_fence_after(); }
+                }
+                mma(d, ks);
+            }
+            st = nst; ph = nph;
+        }
+        if (lane == 0) {
+            const uint32_t pst = st == 0 ? STAGES - 1 : st - 1;
+            ptx::mma_commit(&empty[pst]);
+            ptx::mma_commit(&bar); ptx::mbar_wait(&bar, 0);
+        }
+        __syncwarp();
+        long long t1 = clock64();
+        if (lane == 0) out[0] = t1 - t0;
+    } else if (warp == 0 && (mode & 128)) {
         // converged warp: every lane runs the loop, one elected lane issues
         const uint32_t a0 = ptx::smem_u32(smem), b0 = a0 + 16384;
         constexpr uint32_t ID = make_idesc(128, 128);
@@ -114,4 +161,17 @@ int main() {
     run<5, 4>(128 | 1 | 2 | 32);
     run<2, 4>(128);
     run<5, 8>(128);
+    // which part of the per-tile bookkeeping is exposed (7 MMAs per tile = the head kernel's 112-wide K tiles)
+    run<3, 7>(128);                  // wait + fence + commit
+    run<3, 7>(128 | 2);              // wait + commit
+    run<3, 7>(128 | 1);              // fence + commit
+    run<3, 7>(128 | 1 | 2);          // commit only
+    run<3, 7>(128 | 1 | 32);         // fence only
+    run<3, 7>(128 | 1 | 2 | 32);     // nothing
+    for (int J = 0; J <= 4; ++J) run<3, 7>(256 | (J << 9));     // bookkeeping after the J-th MMA of the tile
+    for (int J = 1; J <= 3; ++J) run<3, 4>(256 | (J << 9));
+    run<5, 7>(128);
+    run<8, 7>(128);
+    run<3, 14>(128);
+    run<3, 28>(128);
 }
