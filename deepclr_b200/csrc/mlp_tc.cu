@@ -824,6 +824,29 @@ head_tc_kernel(HeadArgs a) {
         uint32_t n_done = 0, fin_par = 0;            // bit b: phase parity of fin_done[b]
         const int C0 = a.C0, n = a.n;
         const int cc = C0 / 8, cmid = cc / 2, kc0 = a.Kp[0] / 8;
+        const int cb = half == 0 ? 0 : cmid, ce = half == 0 ? cmid : cc;     // my feature chunks of a row
+        // The NEXT tile's row half travels global -> registers while the last layer runs (these warps mostly wait then):
+        // loaded at build time the 64 KB of a tile arrive through the LSU at ~15 B/cycle and cost 5-7 k cycles of every
+        // tile (tools/head_trace.py).  HEAD_PRE chunks per thread, i.e. C0 = 256; other widths load at build time.
+        constexpr int HEAD_PRE = 16;
+        const bool can_pre = ce - cb == HEAD_PRE;
+        uint4 pre[HEAD_PRE];
+        float pre_xyz[3] = {0.f, 0.f, 0.f};
+        auto prefetch_rows = [&](const int t) {
+            const int tb = t / a.tiles_per_pair;
+            const int tpt = (t - tb * a.tiles_per_pair) * 128 + r;
+            if (tpt < n) {
+                const size_t row = (size_t)tb * n + tpt;
+                const uint4 *f = reinterpret_cast<const uint4 *>(a.feat + row * C0) + cb;
+#pragma unroll
+                for (int i = 0; i < HEAD_PRE; ++i) pre[i] = __ldg(f + i);
+                if (half == 1) {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) pre_xyz[i] = __ldg(a.xyz + row * 3 + i);
+                }
+            }
+        };
+        if (can_pre && (int)blockIdx.x < a.num_tiles) prefetch_rows(blockIdx.x);
         for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * 128;
@@ -832,19 +855,27 @@ head_tc_kernel(HeadArgs a) {
             if (tid == 0) TRACE(tr0);
             // ---- input rows: [motion feat (C0) | xyz hi,hi,lo | 0]; half 0 writes the first feature chunks, half 1
             //      the rest, the coordinates and the padding
-            const int cb = half == 0 ? 0 : cmid, ce = half == 0 ? cmid : cc;
             if (pt < n) {
                 const size_t row = (size_t)b * n + pt;
-                const uint4 *f = reinterpret_cast<const uint4 *>(a.feat + row * C0);
+                if (can_pre) {
+#pragma unroll
+                    for (int i = 0; i < HEAD_PRE; ++i)
+                        st_shared_v4(act_row + (cb + i) * TC_LBO, pre[i].x, pre[i].y, pre[i].z, pre[i].w);
+                } else {
+                    const uint4 *f = reinterpret_cast<const uint4 *>(a.feat + row * C0);
 #pragma unroll 8
-                for (int c = cb; c < ce; ++c) {
-                    const uint4 u = __ldg(f + c);
-                    st_shared_v4(act_row + c * TC_LBO, u.x, u.y, u.z, u.w);
+                    for (int c = cb; c < ce; ++c) {
+                        const uint4 u = __ldg(f + c);
+                        st_shared_v4(act_row + c * TC_LBO, u.x, u.y, u.z, u.w);
+                    }
                 }
                 if (half == 1) {
-                    const float *p3 = a.xyz + row * 3;
-                    store_coord_chunks<T16>(act_row + cc * TC_LBO, act_row + (cc + 1) * TC_LBO, __ldg(p3),
-                                            __ldg(p3 + 1), __ldg(p3 + 2));
+                    if (!can_pre) {
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) pre_xyz[i] = __ldg(a.xyz + row * 3 + i);
+                    }
+                    store_coord_chunks<T16>(act_row + cc * TC_LBO, act_row + (cc + 1) * TC_LBO, pre_xyz[0], pre_xyz[1],
+                                            pre_xyz[2]);
                     for (int c = cc + 2; c < kc0; ++c) st_shared_v4(act_row + c * TC_LBO, 0u, 0u, 0u, 0u);
                 }
             } else {
@@ -870,6 +901,7 @@ head_tc_kernel(HeadArgs a) {
                 if (tid == 0) TRACE(tr0 + 3 + l * 2);
                 ptx::mbar_arrive(act_ready);
             }
+            if (can_pre && tile + (int)gridDim.x < a.num_tiles) prefetch_rows(tile + gridDim.x);
             // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points.
             //      The halves split the 128 columns; both contribute through atomicMax.
             const int nvalid = min(128, n - p0);
