@@ -219,10 +219,23 @@ int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B,
 }
 
 // ------------------------------------------------------------------ kNN
+// General kernel (any Nx, k <= 128).  A warp owns KNN_QPW queries; the candidates pass through shared memory in tiles of
+// 1024 (structure of arrays, so a lane reads two neighbouring candidates per 8-byte load and evaluates them with one
+// packed f32x2 instruction per step, each half rounded exactly like the scalar expression).  The k best so far live in
+// shared memory as sorted keys (d bits << 32 | index: "ascending d^2, ties -> lower index", the oracle's order).  After
+// the first tile the bar is the current k-th distance: a tile contributes only the candidates at or under it -- on
+// unordered clouds ~k ln(Nx / k) of them over ALL later tiles -- so most tiles cost their 32 distances per lane, one
+// count and a vote.  The few survivors are compacted and merged with the current winners by k rounds of a warp minimum
+// over at most four keys per lane.  A tile with too many survivors (the first one; later ones while the bar is loose, as on
+// clouds stored in scan order) first tightens the bar with its own k-th smallest lane minimum; only if even that leaves too
+// many (masses of ties) the k minima are extracted from all of its keys.  16384 x 16384 x 8 clouds, k = 20: 23 ms with the
+// per-tile full extraction only.
 constexpr int KNN_WARPS = 8;
+constexpr int KNN_QPW = 2;                  // queries per warp (share a staged tile)
 constexpr int KNN_KPL = 32;                 // keys per lane per tile
 constexpr int KNN_TILE = 32 * KNN_KPL;      // 1024 candidates per tile
 constexpr int KNN_MAXK = 128;
+constexpr int KNN_CAP = 128;                // merge capacity: current winners + survivors of a tile
 
 __device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
     uint32_t hi = (uint32_t)(v >> 32);
@@ -232,77 +245,182 @@ __device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
     return ((uint64_t)mhi << 32) | mlo;
 }
 
-__global__ void __launch_bounds__(KNN_WARPS * 32)
+__global__ void __launch_bounds__(KNN_WARPS * 32, 3)
 knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int Ny, int k,
            int64_t *__restrict__ row_out, int64_t *__restrict__ col_out, int32_t *__restrict__ col_local,
            float4 *__restrict__ nbr4) {
-    __shared__ float s_c[KNN_TILE * 3];
-    __shared__ uint64_t s_win[KNN_WARPS][KNN_MAXK];
+    __shared__ __align__(8) float s_x[KNN_TILE], s_y[KNN_TILE], s_z[KNN_TILE];
+    __shared__ uint64_t s_win[KNN_WARPS][KNN_QPW][KNN_MAXK];
+    __shared__ uint64_t s_cand[KNN_WARPS][KNN_CAP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.y;
-    const int q = blockIdx.x * KNN_WARPS + warp;
-    const bool active = q < Ny;
+    const int q0 = (blockIdx.x * KNN_WARPS + warp) * KNN_QPW;
     const float *xb = x + (size_t)b * Nx * 3;
-    const size_t gy = (size_t)b * Ny + (active ? q : 0);
-    const float qx = __ldg(y + gy * 3), qy = __ldg(y + gy * 3 + 1), qz = __ldg(y + gy * 3 + 2);
     const uint64_t KMAX = ~0ull;
+    float qx[KNN_QPW], qy[KNN_QPW], qz[KNN_QPW];
+    uint32_t bar[KNN_QPW];                                          // bits of the k-th best distance so far
+#pragma unroll
+    for (int qi = 0; qi < KNN_QPW; ++qi) {
+        const size_t gy = (size_t)b * Ny + min(q0 + qi, Ny - 1);
+        qx[qi] = __ldg(y + gy * 3); qy[qi] = __ldg(y + gy * 3 + 1); qz[qi] = __ldg(y + gy * 3 + 2);
+        bar[qi] = 0xffffffffu;
+    }
     const int ntiles = (Nx + KNN_TILE - 1) / KNN_TILE;
-
     for (int t = 0; t < ntiles; ++t) {
         const int base = t * KNN_TILE;
         const int tile_cnt = min(KNN_TILE, Nx - base);
         __syncthreads();
-        for (int e = tid; e < tile_cnt * 3; e += KNN_WARPS * 32) s_c[e] = __ldg(xb + (size_t)base * 3 + e);
+        for (int j = tid; j < KNN_TILE; j += KNN_WARPS * 32) {
+            const bool ok = j < tile_cnt;
+            const float *c = xb + (size_t)(base + (ok ? j : 0)) * 3;
+            s_x[j] = __ldg(c); s_y[j] = __ldg(c + 1); s_z[j] = __ldg(c + 2);
+        }
         __syncthreads();
-        if (!active) continue;
-        uint64_t keys[KNN_KPL + 4];
 #pragma unroll
-        for (int i = 0; i < KNN_KPL; ++i) {
-            const int j = i * 32 + lane;
-            uint64_t key = KMAX;
-            if (j < tile_cnt) {
-                // torch-cluster: tmp_dist += (x - y)^2 per dimension, x = candidate, y = query
-                float d = sqdist_tc(s_c[j * 3] - qx, s_c[j * 3 + 1] - qy, s_c[j * 3 + 2] - qz);
-                key = ((uint64_t)__float_as_uint(d) << 32) | (uint32_t)(base + j);
-            }
-            keys[i] = key;
-        }
+        for (int qi = 0; qi < KNN_QPW; ++qi) {
+            if (q0 + qi >= Ny) continue;                            // warp-uniform
+            // d[2 i], d[2 i + 1] = tile candidates 2 (i * 32 + lane), + 1.  torch-cluster: tmp_dist += (x - y)^2 per
+            // dimension, x = candidate, y = query
+            float d[KNN_KPL];
+            {
+                uint64_t qxp, qyp, qzp;
+                asm("mov.b64 %0, {%1, %1};" : "=l"(qxp) : "f"(qx[qi]));
+                asm("mov.b64 %0, {%1, %1};" : "=l"(qyp) : "f"(qy[qi]));
+                asm("mov.b64 %0, {%1, %1};" : "=l"(qzp) : "f"(qz[qi]));
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {     // winners carried over from earlier tiles
-            const int w = lane + 32 * c;
-            keys[KNN_KPL + c] = (t > 0 && w < k) ? s_win[warp][w] : KMAX;
-        }
-        __syncwarp();
-        uint64_t lmin = KMAX;
-#pragma unroll
-        for (int i = 0; i < KNN_KPL + 4; ++i) lmin = keys[i] < lmin ? keys[i] : lmin;
-        for (int r = 0; r < k; ++r) {
-            const uint64_t win = warp_min_u64(lmin);
-            if (lane == 0) s_win[warp][r] = win;
-            if (lmin == win) {            // exactly one lane (indices are unique)
-                uint64_t nm = KMAX;
-#pragma unroll
-                for (int i = 0; i < KNN_KPL + 4; ++i) {
-                    uint64_t v = keys[i];
-                    v = (v == win) ? KMAX : v;
-                    keys[i] = v;
-                    nm = v < nm ? v : nm;
+                for (int i = 0; i < KNN_KPL / 2; ++i) {
+                    const int j = 2 * (i * 32 + lane);
+                    uint64_t dx, dy, dz, acc;
+                    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dx) : "l"(*reinterpret_cast<const uint64_t *>(s_x + j)), "l"(qxp));
+                    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dy) : "l"(*reinterpret_cast<const uint64_t *>(s_y + j)), "l"(qyp));
+                    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dz) : "l"(*reinterpret_cast<const uint64_t *>(s_z + j)), "l"(qzp));
+                    asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(acc) : "l"(dx));
+                    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(acc) : "l"(dy), "l"(acc));
+                    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(acc) : "l"(dz), "l"(acc));
+                    asm("mov.b64 {%0, %1}, %2;" : "=f"(d[2 * i]), "=f"(d[2 * i + 1]) : "l"(acc));
                 }
-                lmin = nm;
             }
+            // survivors: existing candidates at or under the bar (d >= 0: its bit image is ordered)
+            uint32_t bq = bar[qi];
+            int cnt = 0;
+#pragma unroll
+            for (int i = 0; i < KNN_KPL; ++i) {
+                const int j = 2 * ((i >> 1) * 32 + lane) + (i & 1);
+                cnt += (j < tile_cnt && __float_as_uint(d[i]) <= bq) ? 1 : 0;
+            }
+            int total = __reduce_add_sync(0xffffffffu, cnt);
+            if (total == 0) continue;                               // warp-uniform: the usual case after a few tiles
+            uint64_t *win = s_win[warp][qi];
+            const int nw = t > 0 ? k : 0;                           // winners carried over
+            if (total + nw > KNN_CAP) {
+                // too many for the merge (always in the first tile; later when the cloud is ordered in space and the
+                // bar is still loose): the tile itself bounds the answer.  T = k-th smallest of the 32 per-lane minima:
+                // at least k of its candidates are <= T, so nothing above min(bar, T) can be among the k best.
+                uint32_t v = 0xffffffffu, T = 0xffffffffu;
+#pragma unroll
+                for (int i = 0; i < KNN_KPL; ++i) {
+                    const int j = 2 * ((i >> 1) * 32 + lane) + (i & 1);
+                    if (j < tile_cnt) v = min(v, __float_as_uint(d[i]));
+                }
+                for (int r = 0; r < k; ++r) {
+                    T = __reduce_min_sync(0xffffffffu, v);
+                    if (v == T) v = 0xffffffffu;
+                }
+                bq = min(bq, T);
+                cnt = 0;
+#pragma unroll
+                for (int i = 0; i < KNN_KPL; ++i) {
+                    const int j = 2 * ((i >> 1) * 32 + lane) + (i & 1);
+                    cnt += (j < tile_cnt && __float_as_uint(d[i]) <= bq) ? 1 : 0;
+                }
+                total = __reduce_add_sync(0xffffffffu, cnt);
+            }
+            if (total + nw <= KNN_CAP) {
+                // ---- merge: compact the survivors, then the k minima of (winners + survivors), <= 4 keys per lane
+                int off = cnt;
+#pragma unroll
+                for (int sft = 1; sft < 32; sft <<= 1) {
+                    const int o = __shfl_up_sync(0xffffffffu, off, sft);
+                    if (lane >= sft) off += o;
+                }
+                off -= cnt;
+                uint64_t *cand = s_cand[warp];
+#pragma unroll
+                for (int i = 0; i < KNN_KPL; ++i) {
+                    const int j = 2 * ((i >> 1) * 32 + lane) + (i & 1);
+                    if (j < tile_cnt && __float_as_uint(d[i]) <= bq)
+                        cand[off++] = ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(base + j);
+                }
+                __syncwarp();
+                uint64_t c[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int e = lane + 32 * u;
+                    c[u] = e < nw ? win[e] : (e - nw < total ? cand[e - nw] : KMAX);
+                }
+                __syncwarp();
+                uint64_t lmin = min(min(c[0], c[1]), min(c[2], c[3]));
+                for (int r = 0; r < k; ++r) {
+                    const uint64_t w = warp_min_u64(lmin);
+                    if (lane == 0) win[r] = w;
+                    if (lmin == w) {                                 // exactly one lane (indices are unique)
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) c[u] = c[u] == w ? KMAX : c[u];
+                        lmin = min(min(c[0], c[1]), min(c[2], c[3]));
+                    }
+                }
+            } else {
+                // ---- all keys of the tile + the winners carried over from earlier tiles
+                uint64_t keys[KNN_KPL + 4];
+#pragma unroll
+                for (int i = 0; i < KNN_KPL; ++i) {
+                    const int j = 2 * ((i >> 1) * 32 + lane) + (i & 1);
+                    keys[i] = j < tile_cnt ? ((uint64_t)__float_as_uint(d[i]) << 32) | (uint32_t)(base + j) : KMAX;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int w = lane + 32 * u;
+                    keys[KNN_KPL + u] = (t > 0 && w < k) ? win[w] : KMAX;
+                }
+                __syncwarp();
+                uint64_t lmin = KMAX;
+#pragma unroll
+                for (int i = 0; i < KNN_KPL + 4; ++i) lmin = keys[i] < lmin ? keys[i] : lmin;
+                for (int r = 0; r < k; ++r) {
+                    const uint64_t w = warp_min_u64(lmin);
+                    if (lane == 0) win[r] = w;
+                    if (lmin == w) {                                 // exactly one lane (indices are unique)
+                        uint64_t nm = KMAX;
+#pragma unroll
+                        for (int i = 0; i < KNN_KPL + 4; ++i) {
+                            uint64_t v = keys[i];
+                            v = (v == w) ? KMAX : v;
+                            keys[i] = v;
+                            nm = v < nm ? v : nm;
+                        }
+                        lmin = nm;
+                    }
+                }
+            }
+            __syncwarp();
+            bar[qi] = (uint32_t)(win[k - 1] >> 32);                 // 0xffffffff while fewer than k candidates were seen
         }
-        __syncwarp();
     }
-    if (!active) return;
-    for (int r = lane; r < k; r += 32) {
-        const uint32_t ci = (uint32_t)s_win[warp][r];
-        const size_t o = gy * k + r;
-        if (row_out) row_out[o] = (int64_t)gy;
-        if (col_out) col_out[o] = (int64_t)((size_t)b * Nx + ci);
-        if (col_local) col_local[o] = (int32_t)ci;
-        if (nbr4) {
-            const float *c = xb + (size_t)ci * 3;
-            nbr4[o] = make_float4(__ldg(c) - qx, __ldg(c + 1) - qy, __ldg(c + 2) - qz, __int_as_float((int)ci));
+#pragma unroll
+    for (int qi = 0; qi < KNN_QPW; ++qi) {
+        if (q0 + qi >= Ny) continue;
+        const size_t gy = (size_t)b * Ny + q0 + qi;
+        for (int r = lane; r < k; r += 32) {
+            const uint32_t ci = (uint32_t)s_win[warp][qi][r];
+            const size_t o = gy * k + r;
+            if (row_out) row_out[o] = (int64_t)gy;
+            if (col_out) col_out[o] = (int64_t)((size_t)b * Nx + ci);
+            if (col_local) col_local[o] = (int32_t)ci;
+            if (nbr4) {
+                const float *c = xb + (size_t)ci * 3;
+                nbr4[o] = make_float4(__ldg(c) - qx[qi], __ldg(c + 1) - qy[qi], __ldg(c + 2) - qz[qi],
+                                      __int_as_float((int)ci));
+            }
         }
     }
 }
@@ -477,7 +595,7 @@ int knn_launch(const float *x, const float *y, int B, int Nx, int Ny, int k, int
         knn_fast_kernel<32><<<fgrid, KNNF_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
         DCLR_LAUNCH_CHECK("knn_fast_kernel");
     } else {
-        knn_kernel<<<dim3(div_up(Ny, KNN_WARPS), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
+        knn_kernel<<<dim3(div_up(Ny, KNN_WARPS * KNN_QPW), B), KNN_WARPS * 32, 0, st>>>(x, y, Nx, Ny, k, row, col, col_local, nbr4);
         DCLR_LAUNCH_CHECK("knn_kernel");
     }
     return DCLR_OK;

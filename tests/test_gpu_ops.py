@@ -144,7 +144,7 @@ def test_ball_query_stride4_two_radii_compact():
 
 
 @pytest.mark.parametrize('B,Nx,Ny,k', [(1, 20, 5, 20), (2, 512, 512, 30), (3, 1024, 1024, 20), (1, 3000, 100, 100),
-                                       (2, 1025, 64, 7)])
+                                       (2, 1025, 64, 7), (1, 16384, 300, 20), (2, 5000, 33, 128)])
 def test_knn_matches_oracle(B, Nx, Ny, k):
     from deepclr_b200.torch_cluster import knn
     rng = np.random.default_rng(Nx + k)
@@ -157,6 +157,27 @@ def test_knn_matches_oracle(B, Nx, Ny, k):
     assert np.array_equal(got, ops.knn(x, y, k, B))
     with pytest.raises(RuntimeError):
         knn(_t(x[:4]), _t(y[:4]), 5)
+
+
+@pytest.mark.parametrize('order', ['towards', 'away', 'ties'])
+def test_knn_general_kernel_on_ordered_candidates(order):
+    """The general kernel prunes a tile by the current k-th distance: candidates sorted TOWARDS the queries make every
+    tile overflow its merge buffer (fallback path), sorted AWAY nothing after the first tile survives, and a cloud of
+    few distinct positions is all ties (lower index first, as torch-cluster's insertion does)."""
+    from deepclr_b200.torch_cluster import knn
+    rng = np.random.default_rng(3)
+    Nx, Ny, k = 6000, 40, 24
+    y = (rng.normal(size=(Ny, 3)) * 0.01).astype(np.float32)
+    x = rng.normal(size=(Nx, 3)).astype(np.float32)
+    r = np.linalg.norm(x, axis=1)
+    if order == 'towards':
+        x = x[np.argsort(-r)]
+    elif order == 'away':
+        x = x[np.argsort(r)]
+    else:
+        x = x[rng.integers(0, 7, Nx)]
+    got = knn(_t(x), _t(y), k).cpu().numpy()
+    assert np.array_equal(got, ops.knn(x, y, k, 1))
 
 
 def test_gather_group_shapes_and_backward(p2):
