@@ -677,6 +677,7 @@ struct HeadArgs {
     const uint16_t *w;      // packed weight tiles in (layer, pair of 128-row blocks, K block, block of the pair) order
     const float *bias;      // biases of the 5 layers, concatenated
     float *pooled;          // [B, out[4]] zero-initialised; max over the points
+    int *ticket;            // {next tile, CTAs finished}: both zero at launch, reset by the last CTA to leave
     int B, n, C0;
     int Kp[HEAD_LAYERS];    // padded input width per layer (multiple of 16)
     int out[HEAD_LAYERS];   // output width per layer (multiple of 128)
@@ -696,9 +697,12 @@ head_tc_kernel(HeadArgs a) {
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_bias + nbias);
     uint64_t *full = s_bar, *empty = s_bar + HEAD_STAGES, *act_ready = empty + HEAD_STAGES,
              *layer_done = act_ready + 1, *fin_done = layer_done + 1, *fin_free = fin_done + HEAD_FIN_BUFS;
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(fin_free + HEAD_FIN_BUFS);
+    uint64_t *next_full = fin_free + HEAD_FIN_BUFS;                      // [2]: s_next[i & 1] holds the tile of iteration i
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(next_full + 2);
+    int *s_next = reinterpret_cast<int *>(s_tmem + 2);
 
     if (tid == 0) {
+        ptx::mbar_init(&next_full[0], 1); ptx::mbar_init(&next_full[1], 1);
         for (int i = 0; i < HEAD_STAGES; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
         ptx::mbar_init(act_ready, HEAD_EPI_WARPS * 32);
         ptx::mbar_init(layer_done, HEAD_MMA_WARPS);
@@ -712,6 +716,14 @@ head_tc_kernel(HeadArgs a) {
     ptx::tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
     constexpr uint32_t IDESC = make_idesc(128, 128, Cvt<T16>::is_bf16);
+    // Tiles are handed out by ticket: iteration 0 of a CTA is tile blockIdx.x, the tile of iteration i + 1 is drawn by
+    // thread 0 while iteration i starts (atomicAdd on a.ticket) and published through s_next / next_full.  A CTA that
+    // gets its SM late (the kernel shares the GPU with the next batch's FPS blocks, 128 SMs wide, on other streams)
+    // then simply draws fewer tiles, instead of holding up the kernel with a static share.
+    auto next_tile = [&](const int i) {                 // tile of iteration i + 1 (every role's lanes may call it)
+        ptx::mbar_wait(&next_full[(i + 1) & 1], (i >> 1) & 1);
+        return *reinterpret_cast<volatile int *>(&s_next[(i + 1) & 1]);
+    };
 
     if (warp >= HEAD_PROD_WARP && warp < HEAD_MMA_WARP) {
         // ===================== weight producers: stream every tile of every layer, once per row tile ===========
@@ -719,7 +731,7 @@ head_tc_kernel(HeadArgs a) {
         const int pq = warp - HEAD_PROD_WARP;
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            for (int ti = 0, tile = blockIdx.x; tile < a.num_tiles; tile = next_tile(ti), ++ti) {
                 const uint8_t *src = reinterpret_cast<const uint8_t *>(a.w);
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     const int nblocks = a.out[l] / 128;
@@ -756,11 +768,11 @@ head_tc_kernel(HeadArgs a) {
             const int q = warp - HEAD_MMA_WARP;
             const uint32_t act_lo = sdesc_lo(ptx::smem_u32(s_act)), wt_lo = sdesc_lo(ptx::smem_u32(s_wt));
             uint32_t it = 0, n_ready = 0, fin_use[2] = {0, 0};
-            for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+            for (int ti = 0, tile = blockIdx.x; tile < a.num_tiles; tile = next_tile(ti), ++ti) {
                 for (int l = 0; l < HEAD_LAYERS; ++l) {
                     ptx::mbar_wait(act_ready, n_ready & 1); ++n_ready;      // this layer's input is in s_act
                     ptx::tc_fence_after();
-                    if (lane == 0 && q == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2);
+                    if (lane == 0 && q == 0) TRACE(ti * 64 + l * 2);
                     const bool last = l == HEAD_LAYERS - 1;
                     const int Kp = a.Kp[l], nblocks = a.out[l] / 128;
                     const int ktiles = (Kp + HEAD_KT - 1) / HEAD_KT;
@@ -810,7 +822,7 @@ head_tc_kernel(HeadArgs a) {
                         it += ktiles * HEAD_MMA_WARPS;
                     }
                     if (!last) ptx::mma_commit_warp(layer_done);       // one arrival per issuing warp
-                    if (lane == 0 && q == 0) TRACE(((tile - blockIdx.x) / gridDim.x) * 64 + l * 2 + 1);
+                    if (lane == 0 && q == 0) TRACE(ti * 64 + l * 2 + 1);
                 }
             }
         }
@@ -847,12 +859,19 @@ head_tc_kernel(HeadArgs a) {
             }
         };
         if (can_pre && (int)blockIdx.x < a.num_tiles) prefetch_rows(blockIdx.x);
-        for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+        int tile_next = 0;
+        for (int ti = 0, tile = blockIdx.x; tile < a.num_tiles; tile = tile_next, ++ti) {
             const int b = tile / a.tiles_per_pair;
             const int p0 = (tile - b * a.tiles_per_pair) * 128;
             const int pt = p0 + r;
-            [[maybe_unused]] const int tr0 = ((tile - blockIdx.x) / gridDim.x) * 64 + 16;
-            if (tid == 0) TRACE(tr0);
+            [[maybe_unused]] const int tr0 = ti * 64 + 16;
+            if (tid == 0) {
+                TRACE(tr0);
+                // draw the tile of iteration ti + 1; everybody has long read slot (ti + 1) & 1 (the tile of iteration
+                // ti - 1, which is complete)
+                s_next[(ti + 1) & 1] = (int)gridDim.x + atomicAdd(a.ticket, 1);
+                ptx::mbar_arrive(&next_full[(ti + 1) & 1]);
+            }
             // ---- input rows: [motion feat (C0) | xyz hi,hi,lo | 0]; half 0 writes the first feature chunks, half 1
             //      the rest, the coordinates and the padding
             if (pt < n) {
@@ -901,7 +920,8 @@ head_tc_kernel(HeadArgs a) {
                 if (tid == 0) TRACE(tr0 + 3 + l * 2);
                 ptx::mbar_arrive(act_ready);
             }
-            if (can_pre && tile + (int)gridDim.x < a.num_tiles) prefetch_rows(tile + gridDim.x);
+            tile_next = next_tile(ti);
+            if (can_pre && tile_next < a.num_tiles) prefetch_rows(tile_next);
             // ---- last layer (transposed): lane = channel, columns = points of the tile; max over the valid points.
             //      The halves split the 128 columns; both contribute through atomicMax.
             const int nvalid = min(128, n - p0);
@@ -933,6 +953,11 @@ head_tc_kernel(HeadArgs a) {
     }
     __syncthreads();
     if (warp == HEAD_MMA_WARP) ptx::tmem_dealloc(tmem_base, 512);
+    if (tid == 0 && atomicAdd(a.ticket + 1, 1) == (int)gridDim.x - 1) {     // every CTA has drawn its last ticket
+        a.ticket[0] = 0;
+        a.ticket[1] = 0;
+        __threadfence();
+    }
 }
 
 // ---------------------------------------------------------------- host side
@@ -944,6 +969,7 @@ struct TcModel {
     float *flow_b = nullptr;
     uint16_t *head_w = nullptr;   // packed head weight tiles
     float *head_b = nullptr;
+    int *tickets = nullptr;       // {next tile, CTAs finished} of head_tc_kernel: zero between launches
     int head_Kp[HEAD_LAYERS], head_out[HEAD_LAYERS], head_act_k;
     size_t flow_smem, head_smem;
     int num_sms;
@@ -981,6 +1007,7 @@ void tc_destroy(TcModel *t) {
     if (t->flow_b) cudaFree(t->flow_b);
     if (t->head_w) cudaFree(t->head_w);
     if (t->head_b) cudaFree(t->head_b);
+    if (t->tickets) cudaFree(t->tickets);
     delete t;
 }
 
@@ -1049,6 +1076,8 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
     }
     TC_CUDA(cudaMalloc(&t->head_w, head_elems * 2));
     TC_CUDA(cudaMalloc(&t->head_b, nbias * sizeof(float)));
+    TC_CUDA(cudaMalloc(&t->tickets, 4 * sizeof(int)));
+    TC_CUDA(cudaMemset(t->tickets, 0, 4 * sizeof(int)));
     p = t->head_w;
     int boff = 0;
     for (int l = 0; l < HEAD_LAYERS; ++l) {
@@ -1066,7 +1095,7 @@ int tc_create(const TcLayerSpec *sp, int F, int k, float radius, int fmt, TcMode
         boff += s.out;
     }
     t->head_smem = (size_t)128 * t->head_act_k * 2 + HEAD_STAGES * HEAD_TILE_BYTES + (size_t)nbias * 4 +
-                   (2 * HEAD_STAGES + 2 + 2 * HEAD_FIN_BUFS) * 8 + 16;
+                   (2 * HEAD_STAGES + 2 + 2 * HEAD_FIN_BUFS + 2) * 8 + 32;
     TC_CUDA(cudaDeviceSynchronize());
     if (t->flow_smem > 232448 || t->head_smem > 232448)
         return bail(fail(DCLR_E_UNSUPPORTED, "tensor-core path: shared memory budget exceeded (%zu / %zu bytes)",
@@ -1119,7 +1148,7 @@ int tc_flow(TcModel *t, const uint16_t *feat, const float4 *nbr, int B, int n, u
 
 int tc_head(TcModel *t, const float *xyz, const uint16_t *motion, int B, int n, float *pooled, cudaStream_t st) {
     HeadArgs ha;
-    ha.feat = motion; ha.xyz = xyz; ha.w = t->head_w; ha.bias = t->head_b; ha.pooled = pooled;
+    ha.feat = motion; ha.xyz = xyz; ha.w = t->head_w; ha.bias = t->head_b; ha.pooled = pooled; ha.ticket = t->tickets;
     ha.B = B; ha.n = n; ha.C0 = t->H3;
     for (int l = 0; l < HEAD_LAYERS; ++l) { ha.Kp[l] = t->head_Kp[l]; ha.out[l] = t->head_out[l]; }
     ha.tiles_per_pair = div_up(n, 128);
