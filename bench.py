@@ -277,7 +277,7 @@ def run_native(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     from deepclr_b200 import sharding
-    from deepclr_b200.models import HostPipeline
+    from deepclr_b200.models import GraphedForward, HostPipeline
     assert torch.cuda.is_available(), 'bench.py (native arm) needs a CUDA device: there is no CPU path'
     torch.cuda.set_device(local_rank)
     dev = torch.device('cuda', local_rank)
@@ -287,7 +287,7 @@ def run_native(args, rank, world, local_rank):
     model, _ = build_model_and_cfg(args.kind)
     model = model.to(dev)
     model.numerics = args.numerics
-    replicas = [model] + [model.replica() for _ in range((args.streams if args.streams > 0 else 4) - 1)]
+    replicas = [model] + [model.replica() for _ in range((args.streams if args.streams > 0 else 8) - 1)]
     gen_kw = dict(partial=True, noise=args.noise) if args.kind == 'modelnet' and args.partial else \
         (dict(noise=args.noise) if args.kind == 'modelnet' else {})
     # strong scaling (BASELINE.json configs[2]): `--pairs` pairs IN TOTAL, contiguous shards of pairs
@@ -309,6 +309,15 @@ def run_native(args, rank, world, local_rank):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def default_lanes(B):
+        """Streams / model replicas per GPU: --streams, else by the size of a step.  The sampling kernel holds one SM per
+        cloud (2 B of 148) for ~0.4 ms whatever the batch, so small steps need more of them in flight.  Measured on one
+        B200 (end to end, pairs/s): 64 pairs per step 2 | 3 | 4 | 6 streams 65.6 k | 66.2 k | 65.8 k | 65.6 k; 8 pairs per
+        step 4 | 8 | 12 | 16 streams 37.4 k | 51.5 k | 50.8 k | 50.0 k."""
+        if args.streams > 0:
+            return args.streams
+        return 4 if B >= 32 else 8
+
     def measure(B, steps, warmup):
         """Resident and end-to-end throughput of this rank's B pairs per step.  Consecutive steps rotate over `--streams`
         model replicas on as many streams (default 4; 1 = no overlap): the sampling kernel occupies one SM per cloud and is
@@ -317,10 +326,23 @@ def run_native(args, rank, world, local_rank):
         32 pairs 37.0 k | 59.8 k | 63.5 k, 16 pairs 22.7 k | 40.0 k | 56.6 k, 8 pairs 12.8 k | 24.4 k | 40.3 k."""
         host = [h[torch.cat([torch.arange(B), args.pairs + torch.arange(B)])].contiguous().pin_memory() for h in full]
         resident = [h.to(dev) for h in host]
-        lanes = args.streams if args.streams > 0 else 4
+        lanes = default_lanes(B)
         models = replicas[:lanes]
         streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)] if lanes > 1 else [None]
         cur = torch.cuda.current_stream(dev)
+        use_graph = os.environ.get('DCLR_GRAPH', '1') == '1'
+        # one CUDA graph per (replica, resident batch), captured over the batch's own storage: a step is one graph launch,
+        # as in the end-to-end arm -- at 8 pairs per step the ~110 plain launches of a forward cost more CPU time than the
+        # step takes on the GPU
+        graphs = {}
+
+        def forward(i):
+            key = (i % lanes, i % ROTATE)
+            if not use_graph:
+                return models[key[0]](resident[key[1]])
+            if key not in graphs:
+                graphs[key] = GraphedForward(models[key[0]], resident[key[1]], alias_input=True)
+            return graphs[key].replay()
 
         def run_resident(n):
             for s in streams:
@@ -330,14 +352,19 @@ def run_native(args, rank, world, local_rank):
                 s = streams[i % lanes]
                 with torch.no_grad():
                     if s is None:
-                        models[0](resident[i % ROTATE])
+                        forward(i)
                     else:
                         with torch.cuda.stream(s):
-                            models[i % lanes](resident[i % ROTATE])
+                            forward(i)
             for s in streams:
                 if s is not None:
                     cur.wait_stream(s)
 
+        if use_graph:                      # capture every (replica, batch) combination outside the timed region
+            with torch.no_grad():
+                for i in range(lanes * ROTATE):
+                    forward(i)
+            torch.cuda.synchronize(dev)
         run_resident(warmup)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -354,7 +381,6 @@ def run_native(args, rank, world, local_rank):
 
         # end to end through the public host-buffer API: H2D of every step's inputs from pinned memory and D2H of its poses
         # inside the timed region (deepclr_b200.models.HostPipeline, forward replayed from CUDA graphs)
-        use_graph = os.environ.get('DCLR_GRAPH', '1') == '1'
         pipe = HostPipeline(model, depth=2 * lanes, use_cuda_graph=use_graph, replicas=lanes)
         pipe.run_all(host[i % ROTATE] for i in range(max(2 * lanes + 1, warmup // 2)))
         pipe.h2d_bytes = pipe.d2h_bytes = 0
