@@ -56,16 +56,14 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
                 float *__restrict__ new_xyz_out) {
     extern __shared__ __align__(16) float smem[];
     constexpr int CAP = 64 * NW * PP;
-    constexpr int T = NW * 32;
     constexpr int WSTRIDE = 64 * NW;
     constexpr int NPAIR = MP * (MP - 1) / 2;
-    constexpr int TCOLS = (NW / 4) * 2 * PP < 32 ? 32 : (NW / 4) * 2 * PP;     // 128 for 16384 records
+    constexpr int TCOLS = (NW / 4) * 4 * PP < 32 ? 32 : (NW / 4) * 4 * PP;     // 256 for 16384 records: {t lo, t hi, tie ranks, -}
     static_assert(NW % 4 == 0 && PP <= 32 && NW <= 32 && MP >= 1 && MP <= NW && NPAIR <= 32, "shape");
     static_assert((TCOLS & (TCOLS - 1)) == 0 && TCOLS <= 512, "TMEM columns: power of two");
     float *s_x = smem, *s_y = smem + CAP, *s_z = smem + 2 * CAP;
-    uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem + 3 * CAP);             // tie rank of the original index
     // warp entries [2][NW] x {value^sign, ~key, bound, -}, {x, y, z, -}; per warp the first MP winners in order [NW][MP] x same
-    int4 *s_slot = reinterpret_cast<int4 *>(s_idx + CAP);
+    int4 *s_slot = reinterpret_cast<int4 *>(smem + 3 * CAP);
     int4 *s_cand = s_slot + 4 * NW;
     int *s_start = reinterpret_cast<int *>(s_cand);                              // (both only live before the first round)
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_cand) + 1;
@@ -76,61 +74,68 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
     if (new_xyz_out) new_xyz_out += (size_t)b * npoint * 3;
 
     if (warp == 0) ptx::tmem_alloc(s_tmem, TCOLS);
-    // stage the cloud: 8 independent 16-byte loads in flight per thread (the loop was one exposed L2 round trip per record)
-    for (int k0 = tid; k0 < CAP; k0 += 8 * T) {
-        float4 r[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int k = k0 + u * T;
-            r[u] = k < N ? __ldg(sorted + k) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int k = k0 + u * T;
-            if (k >= CAP) break;
-            const int oi = __float_as_int(r[u].w);
-            s_x[k] = r[u].x; s_y[k] = r[u].y; s_z[k] = r[u].z;
-            s_idx[k] = oi < 0 ? (uint16_t)0xffffu : (uint16_t)(tie_ref ? fb_rank16(oi) : oi);   // tie order (fb_rank16)
-            if (oi == 0) *s_start = k;
-        }
-    }
+    if (tid == 0) *s_start = 0;
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
-    // this thread's t of bucket i: TMEM lane (32 (warp % 4) + lane), columns tcol + 2 i, + 1
+    // this thread's state of bucket i: TMEM lane (32 (warp % 4) + lane), columns tcol + 4 i: t of its two points and their
+    // tie ranks.  (The ranks used to sit in 32 KB of shared memory; without them the CTA leaves ~30 KB of the SM to the
+    // small kernels of other streams, which can then run beside this latency-bound one.)
     const uint32_t tmem_base = *s_tmem;
-    const uint32_t tcol = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * 2 * PP);
+    const uint32_t tcol = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * 4 * PP);
 
-    // ---- per-bucket metadata (lane i < PP <-> the warp's i-th bucket): box, max t, key of the max, second max (bound)
+    // ---- stage the cloud (every lane loads the two records it owns: 1 KB contiguous per warp and bucket, 8 loads in flight)
+    //      + per-bucket metadata (lane i < PP <-> the warp's i-th bucket): box, max t, key of the max, second max (bound)
     float blx = 0.f, bly = 0.f, blz = 0.f, bhx = 0.f, bhy = 0.f, bhz = 0.f, bm = -1.0f, bm2 = -1.0f;
     uint32_t bkey = 0xffffff00u | (uint32_t)warp;
     const uint32_t rec0 = (uint32_t)(64 * warp + 2 * lane);                    // record of pair 0; pair i: + WSTRIDE * i
     const uint32_t ax = ptx::smem_u32(s_x) + rec0 * 4, ay = ptx::smem_u32(s_y) + rec0 * 4,
-                   az = ptx::smem_u32(s_z) + rec0 * 4, ai = ptx::smem_u32(s_idx) + rec0 * 2;
-    for (int i = 0; i < PP; ++i) {
-        const int p = (int)rec0 + WSTRIDE * i;
-        const bool v0 = p < N, v1 = p + 1 < N;
-        // -1 can never win (reference: best starts at -1, strict >)
-        ptx::tmem_st2(tcol + 2 * i, __float_as_uint(v0 ? 1e10f : -1.0f), __float_as_uint(v1 ? 1e10f : -1.0f));
-        float lo[3], hi[3];
-        const float c0[3] = {s_x[p], s_y[p], s_z[p]}, c1[3] = {s_x[p + 1], s_y[p + 1], s_z[p + 1]};
+                   az = ptx::smem_u32(s_z) + rec0 * 4;
+    constexpr int UNR = PP % 4 == 0 ? 4 : 1;
+    for (int i0 = 0; i0 < PP; i0 += UNR) {
+        float4 ra[UNR], rb[UNR];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            lo[a] = fminf(v0 ? c0[a] : FLT_MAX, v1 ? c1[a] : FLT_MAX);
-            hi[a] = fmaxf(v0 ? c0[a] : -FLT_MAX, v1 ? c1[a] : -FLT_MAX);
+        for (int u = 0; u < UNR; ++u) {
+            const int p = (int)rec0 + WSTRIDE * (i0 + u);
+            ra[u] = p < N ? __ldg(sorted + p) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            rb[u] = p + 1 < N ? __ldg(sorted + p + 1) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        }
 #pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) {
-                lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], d));
-                hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], d));
+        for (int u = 0; u < UNR; ++u) {
+            const int i = i0 + u;
+            const int p = (int)rec0 + WSTRIDE * i;
+            const int o0 = __float_as_int(ra[u].w), o1 = __float_as_int(rb[u].w);
+            const bool v0 = o0 >= 0, v1 = o1 >= 0;
+            s_x[p] = ra[u].x; s_y[p] = ra[u].y; s_z[p] = ra[u].z;
+            s_x[p + 1] = rb[u].x; s_y[p + 1] = rb[u].y; s_z[p + 1] = rb[u].z;
+            if (o0 == 0) *s_start = p;
+            if (o1 == 0) *s_start = p + 1;
+            const uint32_t r0 = v0 ? (uint32_t)(tie_ref ? fb_rank16(o0) : o0) & 0xffffu : 0xffffu;     // tie order (fb_rank16)
+            const uint32_t r1 = v1 ? (uint32_t)(tie_ref ? fb_rank16(o1) : o1) & 0xffffu : 0xffffu;
+            // -1 can never win (reference: best starts at -1, strict >)
+            ptx::tmem_st4(tcol + 4 * i, __float_as_uint(v0 ? 1e10f : -1.0f), __float_as_uint(v1 ? 1e10f : -1.0f),
+                          r0 | (r1 << 16), 0u);
+            float lo[3], hi[3];
+            const float c0[3] = {ra[u].x, ra[u].y, ra[u].z}, c1[3] = {rb[u].x, rb[u].y, rb[u].z};
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                lo[a] = fminf(v0 ? c0[a] : FLT_MAX, v1 ? c1[a] : FLT_MAX);
+                hi[a] = fmaxf(v0 ? c0[a] : -FLT_MAX, v1 ? c1[a] : -FLT_MAX);
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) {
+                    lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], d));
+                    hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], d));
+                }
+            }
+            const bool any = __any_sync(0xffffffffu, v0);
+            if (lane == i) {
+                blx = lo[0]; bly = lo[1]; blz = lo[2]; bhx = hi[0]; bhy = hi[1]; bhz = hi[2];
+                bm = any ? 1e10f : -1.0f;          // 1e10 forces the first update; key and bm2 are set there
+                bm2 = bm;
             }
         }
-        const bool any = __any_sync(0xffffffffu, v0);
-        if (lane == i) {
-            blx = lo[0]; bly = lo[1]; blz = lo[2]; bhx = hi[0]; bhy = hi[1]; bhz = hi[2];
-            bm = any ? 1e10f : -1.0f;          // 1e10 forces the first update; key and bm2 are set there
-            bm2 = bm;
-        }
     }
+    __syncthreads();                               // *s_start and everybody's coordinates
     ptx::tmem_st_wait();
 
     // candidate pair (pl, pr), pl < pr, tested by this lane: pair index p = pr (pr - 1) / 2 + pl
@@ -189,10 +194,10 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
                 uint32_t id2[2], tlb[2], thb[2];
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
+                    uint32_t pad;
                     X[u] = fb_lds64(ax + iu[u] * (WSTRIDE * 4)); Y[u] = fb_lds64(ay + iu[u] * (WSTRIDE * 4));
                     Z[u] = fb_lds64(az + iu[u] * (WSTRIDE * 4));
-                    id2[u] = fb_lds32(ai + iu[u] * (WSTRIDE * 2));
-                    ptx::tmem_ld2(tcol + 2 * iu[u], tlb[u], thb[u]);
+                    ptx::tmem_ld4(tcol + 4 * iu[u], tlb[u], thb[u], id2[u], pad);
                 }
                 ptx::tmem_ld_wait();
                 int mx[2], mn[2], nlb[2], nhb[2];
@@ -209,7 +214,7 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
                         nl = fminf(dl, nl);
                         nh = fminf(dh, nh);
                     }
-                    ptx::tmem_st2(tcol + 2 * iu[u], __float_as_uint(nl), __float_as_uint(nh));
+                    ptx::tmem_st2(tcol + 4 * iu[u], __float_as_uint(nl), __float_as_uint(nh));
                     nlb[u] = __float_as_int(nl); nhb[u] = __float_as_int(nh);
                     mx[u] = max(nlb[u], nhb[u]);          // integer images: values are >= 0 or exactly -1.0f (negative int)
                     mn[u] = min(nlb[u], nhb[u]);
@@ -339,8 +344,8 @@ fps_tmem_kernel(const float4 *__restrict__ sorted, int N, int npoint, int tie_re
 template <int NW, int PP, int MP>
 static int launch_tmem(const float4 *sorted, int B, int N, int npoint, int tie_ref, int32_t *idx, float *nx,
                        cudaStream_t st) {
-    const size_t smem = (size_t)64 * NW * PP * 14 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4);
-    static_assert((size_t)64 * NW * PP * 14 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4) <= 232448, "shared memory");
+    const size_t smem = (size_t)64 * NW * PP * 12 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4);
+    static_assert((size_t)64 * NW * PP * 12 + (size_t)(4 * NW + 2 * NW * MP) * sizeof(int4) <= 232448, "shared memory");
     auto kern = fps_tmem_kernel<NW, PP, MP>;
     DCLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<B, NW * 32, smem, st>>>(sorted, N, npoint, tie_ref, idx, nx);
