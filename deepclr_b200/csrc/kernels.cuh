@@ -59,6 +59,12 @@ struct SaArgs {
     int N, M, ld_out, nscales;
 };
 int sa_mlp_launch(const SaArgs &a, int B, int cin, const int *h, cudaStream_t st);
+// sa_tc.cu: the same stage on the tcgen05 tensor cores (fp16 hi/lo split operands, fp32-class results) for dense
+// neighbourhoods; w_dev = 2 x sa_tc_weight_bytes() / 2 packed by sa_tc_pack_scale (host) per scale
+size_t sa_tc_weight_bytes();
+void sa_tc_pack_scale(const float *w_host, int cin, uint16_t *img);
+int sa_tc_launch(const SaArgs &a, const uint16_t *w_dev, int B, int cin, cudaStream_t st);
+int sa_count_rows_launch(const int32_t *cnt, size_t n, unsigned long long *rows, cudaStream_t st);
 
 // dense_f32.cu
 int linear_f32_launch(const float *X, int ldx, const float *W, const float *b, float *Y, int ldy, int M, int N, int K,

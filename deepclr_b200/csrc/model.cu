@@ -5,6 +5,7 @@
 #include "mlp_tc.cuh"
 #include <nvtx3/nvToolsExt.h>
 #include <new>
+#include <stdlib.h>
 #include <vector>
 
 struct dclr_model {
@@ -13,6 +14,9 @@ struct dclr_model {
     float *d_w = nullptr;            // all parameters, state-dict order
     size_t n_w = 0;
     std::vector<float> sa_w_host[2];   // SA MLP parameters, host copy (passed as kernel parameters)
+    uint16_t *sa_tc_w = nullptr;       // the same as packed fp16 hi/lo images for sa_tc_kernel (sa_tc.cu)
+    unsigned long long *sa_rows = nullptr;   // device counter of the density probe
+    int sa_dense = -1, sa_dense_G = 0, sa_dense_N = 0;   // -1 unknown | 0 sparse: sa_mlp_kernel | 1 dense: sa_tc_kernel, for (G, N)
     struct Lin { const float *W, *b; int out, in; };
     Lin merge[3], outc[5], lin[2], fin;
     int numerics = 0;
@@ -42,6 +46,8 @@ struct dclr_model {
 };
 
 namespace dclr {
+
+constexpr int SA_TC_MIN_ROWS_PER_CENTRE = 8;   // mean genuine rows per (centre, scale) from which sa_tc_kernel is used
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -222,7 +228,36 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
         s.idx[i] = m->bq_idx[i]; s.cnt[i] = m->bq_cnt[i]; s.ns[i] = a.nsamples[i < a.num_scales ? i : 0];
         s.w_host[i] = m->sa_w_host[i < a.num_scales ? i : 0].data();
     }
-    DCLR_TRY(sa_mlp_launch(s, G, a.input_dim, a.sa_mlp[0], st));
+    // Which kernel?  fp32 numerics: always the fp32 SIMT kernel.  16-bit modes: the tensor-core kernel (fp16 hi/lo split,
+    // fp32-class results) when the neighbourhoods are dense -- measured once per (clouds, points) shape of a handle: the
+    // first call counts the genuine rows (bq_cnt), reads the total back (one synchronisation, never during a stream
+    // capture) and keeps the decision.  Crossover: tools/sa_density_sweep.py.  DCLR_SA_ROUTE=simt|tc overrides.
+    int route = 0;
+    if (m->numerics != 0) {
+        const char *env = getenv("DCLR_SA_ROUTE");
+        if (env && env[0] == 't') route = 1;
+        else if (env && env[0] == 's') route = 0;
+        else {
+            if (m->sa_dense < 0 || m->sa_dense_G != G || m->sa_dense_N != N) {
+                cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+                DCLR_CUDA(cudaStreamIsCapturing(st, &cap));
+                if (cap == cudaStreamCaptureStatusNone) {
+                    unsigned long long rows = 0;
+                    DCLR_CUDA(cudaMemsetAsync(m->sa_rows, 0, sizeof(rows), st));
+                    for (int i = 0; i < a.num_scales; ++i)
+                        DCLR_TRY(sa_count_rows_launch(m->bq_cnt[i], (size_t)G * a.npoint, m->sa_rows, st));
+                    DCLR_CUDA(cudaMemcpyAsync(&rows, m->sa_rows, sizeof(rows), cudaMemcpyDeviceToHost, st));
+                    DCLR_CUDA(cudaStreamSynchronize(st));
+                    m->sa_dense = rows >= (unsigned long long)SA_TC_MIN_ROWS_PER_CENTRE * G * a.npoint * a.num_scales;
+                    m->sa_dense_G = G; m->sa_dense_N = N;
+                    m->last_launches -= a.num_scales;              // (the probe is not part of a steady-state forward)
+                }
+            }
+            route = m->sa_dense > 0;
+        }
+    }
+    if (route) DCLR_TRY(sa_tc_launch(s, m->sa_tc_w, G, a.input_dim, st));
+    else DCLR_TRY(sa_mlp_launch(s, G, a.input_dim, a.sa_mlp[0], st));
     return DCLR_OK;
 }
 
@@ -382,6 +417,18 @@ extern "C" int dclr_model_create(const dclr_arch *arch, const float *weights, si
         const size_t end = s + 1 < a.num_scales ? sa_off[s + 1] : w_off[first_dense];
         m->sa_w_host[s].assign(weights + sa_off[s], weights + end);
     }
+    {
+        // tensor-core images of the SA weights (used in the 16-bit numerics modes on dense neighbourhoods)
+        std::vector<uint16_t> img(sa_tc_weight_bytes() / sizeof(uint16_t), 0);
+        for (int s = 0; s < a.num_scales; ++s) sa_tc_pack_scale(m->sa_w_host[s].data(), a.input_dim, img.data() + s * (img.size() / 2));
+        e = cudaMalloc(&m->sa_tc_w, sa_tc_weight_bytes());
+        if (e == cudaSuccess) e = cudaMemcpy(m->sa_tc_w, img.data(), sa_tc_weight_bytes(), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMalloc(&m->sa_rows, sizeof(unsigned long long));
+        if (e != cudaSuccess) {
+            dclr_model_destroy(m);
+            return fail(DCLR_E_CUDA, "dclr_model_create: %s", cudaGetErrorString(e));
+        }
+    }
     size_t q = first_dense;
     auto lin = [&](int o, int i) { dclr_model::Lin L{m->d_w + w_off[q], m->d_w + b_off[q], o, i}; ++q; return L; };
     cin = m->nmerge_in;
@@ -403,6 +450,8 @@ extern "C" void dclr_model_destroy(dclr_model *m) {
     }
     if (m->ws) cudaFree(m->ws);
     if (m->d_w) cudaFree(m->d_w);
+    if (m->sa_tc_w) cudaFree(m->sa_tc_w);
+    if (m->sa_rows) cudaFree(m->sa_rows);
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);
     if (m->ev_fps) cudaEventDestroy(m->ev_fps);

@@ -7,6 +7,8 @@
   * the stage-level C entries (dclr_sa_msg_fused / dclr_flow_embed_fused / dclr_pose_head_fused) against the whole path;
   * CUDA graphs that outlive a workspace re-allocation or a weight update.
 Tolerances are those of tests/test_gpu_model.py."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -172,3 +174,38 @@ def test_host_pipeline_with_replicas_equals_plain(use_graph):
     assert len(plain) == len(multi) == 11
     for a, b in zip(plain, multi):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('golden,kind,n', [('modelnet_b2', 'modelnet', None), ('kitti_small_b2', 'kitti', None),
+                                           ('kitti_b1', 'kitti', 16384)])
+def test_sa_tensor_core_kernel_equals_simt_kernel(golden, kind, n):
+    """sa_tc_kernel (tcgen05, fp16 hi/lo split operands) against sa_mlp_kernel (fp32 FFMA) on the same centres and
+    neighbour lists: fp32-class agreement (the split carries 22 significant bits), dense ModelNet-shaped and sparse
+    KITTI-shaped neighbourhoods, input_dim 3 and 4, partial last block of centres."""
+    from deepclr_b200 import synth
+    g = load_golden(golden)
+    model, _ = build_from_golden(g, DEV)
+    model.numerics = 'fp16'
+    n = int(g['n']) if n is None else n
+    x = torch.from_numpy(synth.batch(kind, 3, 33, n=n)).to(DEV)
+    with torch.no_grad():
+        model(x)
+        native = model._native
+        _, feat, _ = native.forward_pairs(x, want_feat=True, want_motion=True)
+        new_xyz = feat[:, :3].transpose(1, 2).contiguous()
+        old = os.environ.get('DCLR_SA_ROUTE')
+        try:
+            os.environ['DCLR_SA_ROUTE'] = 'simt'
+            ref = native.sa_msg(x, new_xyz)
+            os.environ['DCLR_SA_ROUTE'] = 'tc'
+            got = native.sa_msg(x, new_xyz)
+            again = native.sa_msg(x, new_xyz)
+        finally:
+            if old is None:
+                os.environ.pop('DCLR_SA_ROUTE', None)
+            else:
+                os.environ['DCLR_SA_ROUTE'] = old
+    assert torch.equal(got, again)                                   # atomicMax on integer images: order independent
+    scale = float(ref.abs().max())
+    assert scale > 0
+    assert float((got - ref).abs().max()) <= 2e-6 * scale + 1e-7
