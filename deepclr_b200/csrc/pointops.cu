@@ -485,11 +485,23 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
                 asm("min.f32 %0, %0, %1, %2;" : "+f"(lmin) : "f"(d[2 * i]), "f"(d[2 * i + 1]));
             }
         }
-        // threshold: k rounds of "take the smallest remaining lane minimum" (d >= 0, so its bit image is ordered)
-        uint32_t v = __float_as_uint(lmin), T = 0;
+        // threshold: k rounds of "take the smallest remaining lane minimum" (d >= 0, so its bit image is ordered).
+        // With k close to 32 the k-th smallest of 32 lane minima is a weak bound (k = 30 on 512 candidates: ~100
+        // survivors, the slow selection below); there every lane offers its TWO smallest distances instead, and the
+        // k-th smallest of those 64 real candidates is close to the true k-th distance (~35 survivors).
+        uint32_t v = __float_as_uint(lmin), v2 = 0xffffffffu, T = 0;
+        if (k > 24) {                                           // warp-uniform
+            float m1 = INFINITY, m2 = INFINITY;
+#pragma unroll
+            for (int i = 0; i < KPL; ++i) {
+                m2 = fminf(m2, fmaxf(m1, d[i]));
+                m1 = fminf(m1, d[i]);
+            }
+            v2 = __float_as_uint(m2);
+        }
         for (int r = 0; r < k; ++r) {
             T = __reduce_min_sync(0xffffffffu, v);
-            if (v == T) v = 0xffffffffu;
+            if (v == T) { v = v2; v2 = 0xffffffffu; }
         }
         // count + compact everything with d <= T
         int cnt = 0;
