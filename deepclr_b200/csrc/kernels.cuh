@@ -32,6 +32,7 @@ int ball_query_launch(const float *new_xyz, const float *pts, int stride, int B,
                       cudaStream_t st);
 // ballgrid.cu: grid-accelerated ball query for large clouds; *used = 0 when the shape is not handled (then call
 // ball_query_launch).  ws must hold ball_grid_workspace_bytes(B, N) bytes.
+constexpr int BG_MIN_N = 1024;          // smallest cloud that takes the uniform grid (ballgrid.cu)
 size_t ball_grid_workspace_bytes(int B, int N);
 // phase: the grid build reads only the cloud, so the model runs it on a side stream next to FPS (BG_PHASE_BUILD, new_xyz
 // unused) and the query after both (BG_PHASE_QUERY); *used is the same for every phase of a shape.

@@ -676,7 +676,7 @@ extern "C" int dclr_ball_query(const float *new_xyz, const float *pts, int pt_st
     int32_t *idx[1] = {idx_out};
     int32_t *cnt[1] = {cnt_out};
     cudaStream_t st = (cudaStream_t)stream;
-    if (N >= 2048) {                                       // large clouds: uniform-grid candidate pruning (ballgrid.cu)
+    if (N >= BG_MIN_N) {                                   // large clouds: uniform-grid candidate pruning (ballgrid.cu)
         void *ws = nullptr;
         { int rc_ = scratch_alloc(&ws, ball_grid_workspace_bytes(B, N), st); if (rc_ != DCLR_OK) return rc_; }
         int used = 0;
