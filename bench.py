@@ -313,10 +313,13 @@ def run_native(args, rank, world, local_rank):
         """Streams / model replicas per GPU: --streams, else by the size of a step.  The sampling kernel holds one SM per
         cloud (2 B of 148) for ~0.4 ms whatever the batch, so small steps need more of them in flight.  Measured on one
         B200 (end to end, pairs/s): 64 pairs per step 2 | 3 | 4 | 6 streams 65.6 k | 66.2 k | 65.8 k | 65.6 k; 8 pairs per
-        step 4 | 8 | 12 | 16 streams 37.4 k | 51.5 k | 50.8 k | 50.0 k."""
+        step 4 | 8 | 12 | 16 streams 37.4 k | 51.5 k | 50.8 k | 50.0 k.  Eight ranks on one box (8 pairs per GPU and step,
+        resident | end to end): 4 streams 320 k | 267 k, 6 streams 308 k | 316 k, 8 streams 391 k | 235 k -- with eight
+        processes the host side of the end-to-end loop (Python: ~15 stream / event calls per step) competes for the
+        cores, so small steps default to 6."""
         if args.streams > 0:
             return args.streams
-        return 4 if B >= 32 else 8
+        return 4 if B >= 32 else 6
 
     def measure(B, steps, warmup):
         """Resident and end-to-end throughput of this rank's B pairs per step.  Consecutive steps rotate over `--streams`
