@@ -209,3 +209,28 @@ def test_sa_tensor_core_kernel_equals_simt_kernel(golden, kind, n):
     scale = float(ref.abs().max())
     assert scale > 0
     assert float((got - ref).abs().max()) <= 2e-6 * scale + 1e-7
+
+
+@pytest.mark.parametrize('golden,kind,pairs,n', [('kitti_b1', 'kitti', 5, 16384), ('modelnet_b2', 'modelnet', 24, None)])
+def test_forward_is_bit_reproducible_over_repeated_calls(golden, kind, pairs, n):
+    """40 forwards of one batch, alone and with a second replica running other batches on another stream: every result
+    equals the first bit for bit.  Nothing in the path may depend on timing -- tiles drawn by ticket (head), atomicMax
+    pooling (head, tensor-core SA), samples per FPS round, which warp issues which weight tile."""
+    from deepclr_b200 import synth
+    g = load_golden(golden)
+    model, _ = build_from_golden(g, DEV)
+    model.numerics = 'fp16'
+    n = int(g['n']) if n is None else n
+    x = torch.from_numpy(synth.batch(kind, pairs, 71, n=n)).to(DEV)
+    other = [torch.from_numpy(synth.batch(kind, pairs, 72 + i, n=n)).to(DEV) for i in range(2)]
+    rep = model.replica()
+    side = torch.cuda.Stream(device=DEV)
+    with torch.no_grad():
+        first = model(x)[0].clone()
+        for i in range(40):
+            if i >= 20:                                   # the second half shares the GPU with another replica
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    rep(other[i % 2])
+            assert torch.equal(model(x)[0], first), f'call {i} differs'
+        torch.cuda.synchronize()
