@@ -6,9 +6,11 @@
 //    time, so fps_bucket.cu carries one unrolled copy of the update per bucket (32 per warp, ~20 KB of code) and walks a
 //    chain of branches to the touched ones: i-cache misses and taken branches cost more than the update itself (~350 of
 //    ~960 cycles per round).  TMEM is 256 KB per SM of storage that is private to a lane AND addressed by a RUNTIME column
-//    (tcgen05.ld / tcgen05.st .32x32b: lane l of warp w reads its own row l of lane quarter w % 4).  With t of bucket i
-//    in columns 2i, 2i+1 the update is ONE generic loop body over the set bits of the skip mask, two buckets per
-//    iteration so that their load -> distance -> redux chains overlap; no tensor-core instruction is involved.
+//    (tcgen05.ld / tcgen05.st .32x32b: lane l of warp w reads its own row l of lane quarter w % 4).  With the state of
+//    bucket i in columns 4i .. 4i+2 (t of the lane's two points and their two 16-bit tie ranks: one tcgen05.ld.x4) the
+//    update is ONE generic loop body over the set bits of the skip mask, two buckets per iteration so that their
+//    load -> distance -> redux chains overlap; no tensor-core instruction is involved.  Shared memory holds only the
+//    coordinates (193 KB), which leaves ~30 KB of the SM to small kernels of other streams.
 //
 // 2. Up to MP samples per round, EXACTLY.  At the barrier every warp w publishes its best point (value v_w, tie key) and
 //    an upper bound u_w of every OTHER running minimum in the warp.  Sort the NW warp winners c_0 >= c_1 >= ... by

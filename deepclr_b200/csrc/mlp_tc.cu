@@ -646,7 +646,7 @@ flow_tc_kernel(FlowArgs a) {
 constexpr int HEAD_LAYERS = 5;
 // Weight ring shape (overridable for tools/ab.sh).  Every tile costs an exposed mbarrier wait + commit (~115 cycles,
 // tools/micro/mma_ring.cu), so tiles are as wide as the shared-memory budget allows: measured head time per 64 pairs
-// 64 x 5 stages 0.184 ms | 80 x 4 0.174 | 96 x 3 0.168 | 96 x 2 0.192 | 128 x 2 0.177 | **112 x 3 0.163**.
+// 64 x 5 stages 0.184 ms | 80 x 4 0.174 | 96 x 3 0.168 | 96 x 2 0.192 | 128 x 2 0.177 | 112 x 3 0.163 (ONE issuing warp).
 // With two issuing warps (below) stage s belongs to warp s % 2 (tile `it` of the stream sits in stage it % STAGES and
 // belongs to warp it % 2, so STAGES must be even): a consumer then never waits on a stage whose previous occupant was
 // another warp's, and the 1-bit phase parity of its mbarrier cannot alias.  4 x 20 KB.
@@ -654,7 +654,7 @@ constexpr int HEAD_LAYERS = 5;
 #define DCLR_HEAD_KT 80
 #define DCLR_HEAD_STAGES 4
 #endif
-constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 112 = 28 KB)
+constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 80 = 20 KB)
 constexpr int HEAD_STAGES = DCLR_HEAD_STAGES;
 constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
 constexpr int HEAD_EPI_WARPS = 8;                // 4 TMEM lane quarters x 2 column halves
@@ -692,7 +692,7 @@ head_tc_kernel(HeadArgs a) {
     int nbias = 0;
     for (int l = 0; l < HEAD_LAYERS; ++l) nbias += a.out[l];
     uint8_t *s_act = smem;                                              // 128 x act_k x 2
-    uint8_t *s_wt = s_act + (size_t)128 * a.act_k * 2;                  // HEAD_STAGES x 16 KB
+    uint8_t *s_wt = s_act + (size_t)128 * a.act_k * 2;                  // HEAD_STAGES x HEAD_TILE_BYTES
     float *s_bias = reinterpret_cast<float *>(s_wt + HEAD_STAGES * HEAD_TILE_BYTES);
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_bias + nbias);
     uint64_t *full = s_bar, *empty = s_bar + HEAD_STAGES, *act_ready = empty + HEAD_STAGES,
