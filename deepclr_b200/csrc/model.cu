@@ -237,7 +237,11 @@ static int run_set_abstraction(dclr_model *m, const float *x, int G, int N, cuda
         const char *env = getenv("DCLR_SA_ROUTE");
         if (env && env[0] == 't') route = 1;
         else if (env && env[0] == 's') route = 0;
-        else {
+        else if ((long long)G * a.npoint < 148LL * 128) {
+            // small launches (up to 9 KITTI pairs): latency matters, not what shares the SMs with the sampling kernel of
+            // another step, and the tensor kernel is the shorter one at every density (batch 1: 0.030 -> 0.019 ms)
+            route = 1;
+        } else {
             if (m->sa_dense < 0 || m->sa_dense_G != G || m->sa_dense_N != N) {
                 cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
                 DCLR_CUDA(cudaStreamIsCapturing(st, &cap));
