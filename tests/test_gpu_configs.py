@@ -234,3 +234,45 @@ def test_forward_is_bit_reproducible_over_repeated_calls(golden, kind, pairs, n)
                     rep(other[i % 2])
             assert torch.equal(model(x)[0], first), f'call {i} differs'
         torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize('npoint,k', [(100, 20), (77, 9)])
+def test_tensor_core_sa_with_a_partial_block_of_centres(npoint, k):
+    """npoint not a multiple of the 32 centres a CTA of sa_tc_kernel owns (last block partial) and smaller than a tile of
+    the other kernels: both SA kernels agree, and the whole fp16 path agrees with the fp32 path within the fp16 tolerance."""
+    import yaml
+    from deepclr_b200 import synth
+    from deepclr_b200.config.config import Config
+    from deepclr_b200.data.labels import LabelType
+    from deepclr_b200.models.build import ModelType, build_model
+    g = load_golden('kitti_small_b2')
+    cfg = yaml.safe_load(str(g['cfg_yaml']))
+    cfg['params']['cloud_features']['params']['npoint'] = [npoint]
+    cfg['params']['merge']['params']['k'] = k
+    c = Config._from_dict(cfg)
+    c.label_type = LabelType.create(c.label_type)
+    c.model_type = ModelType.create(c.model_type)
+    torch.manual_seed(3)
+    model = build_model(c).eval().to(DEV)
+    x = torch.from_numpy(synth.batch('kitti', 2, 55, n=3000)).to(DEV)
+    with torch.no_grad():
+        model.numerics = 'fp32'
+        y32 = model(x)[0].clone()
+        model.numerics = 'fp16'
+        y16 = model(x)[0].clone()
+        native = model._native
+        _, feat, _ = native.forward_pairs(x, want_feat=True, want_motion=True)
+        new_xyz = feat[:, :3].transpose(1, 2).contiguous()
+        old = os.environ.get('DCLR_SA_ROUTE')
+        try:
+            os.environ['DCLR_SA_ROUTE'] = 'simt'
+            ref = native.sa_msg(x, new_xyz)
+            os.environ['DCLR_SA_ROUTE'] = 'tc'
+            got = native.sa_msg(x, new_xyz)
+        finally:
+            if old is None:
+                os.environ.pop('DCLR_SA_ROUTE', None)
+            else:
+                os.environ['DCLR_SA_ROUTE'] = old
+    assert float((got - ref).abs().max()) <= 2e-6 * float(ref.abs().max()) + 1e-7
+    np.testing.assert_allclose(y16.cpu().numpy(), y32.cpu().numpy(), atol=2e-2)
