@@ -185,30 +185,38 @@ sa_tc_kernel(const SaTcParams a) {
         const int total = s_excl[ST_CB];
         const int32_t *lists = a.idx[s] + ((size_t)b * a.M + c0) * a.ns[s];
         // row `row` of this scale: its centre and the neighbour's point, fetched one tile ahead (index, then the point it
-        // names: two dependent L2 round trips that would otherwise sit in front of every tile)
-        int nci = 0;
+        // names: two dependent L2 round trips that would otherwise sit in front of every tile).
+        // Two stages, because a warp issues in order: the index load's first USE (the point address) would stall it for
+        // an L2 round trip.  fetch_index right after a tile's build, fetch_point one layer later, the point's first use
+        // at the next build.
+        int nci = 0, nk = 0;
         float nin[4] = {0.f, 0.f, 0.f, 0.f};
-        auto fetch_row = [&](const int row) {
+        auto fetch_index = [&](const int row) {
+            nk = 0;
             if (row < total) {
                 int ci = 0;
 #pragma unroll
                 for (int step = 16; step >= 1; step >>= 1)
                     if (s_excl[ci + step] <= row) ci += step;          // last centre whose first row is <= row
                 const int j = row - s_excl[ci];
-                const int k = s_nraw[ci] > 0 ? __ldg(lists + (size_t)ci * a.ns[s] + j) : 0;
-                if (a.cin == 4) {
-                    const float4 v = __ldg(reinterpret_cast<const float4 *>(xb) + k);
-                    nin[0] = v.x; nin[1] = v.y; nin[2] = v.z; nin[3] = v.w;
-                } else {
-                    nin[0] = __ldg(xb + (size_t)k * 3); nin[1] = __ldg(xb + (size_t)k * 3 + 1);
-                    nin[2] = __ldg(xb + (size_t)k * 3 + 2); nin[3] = 0.f;
-                }
+                if (s_nraw[ci] > 0) nk = __ldg(lists + (size_t)ci * a.ns[s] + j);
                 nci = ci;
             } else {
                 nci = 0xff;
             }
         };
-        fetch_row(tid);
+        auto fetch_point = [&]() {
+            if (nci == 0xff) return;
+            if (a.cin == 4) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(xb) + nk);
+                nin[0] = v.x; nin[1] = v.y; nin[2] = v.z; nin[3] = v.w;
+            } else {
+                nin[0] = __ldg(xb + (size_t)nk * 3); nin[1] = __ldg(xb + (size_t)nk * 3 + 1);
+                nin[2] = __ldg(xb + (size_t)nk * 3 + 2); nin[3] = 0.f;
+            }
+        };
+        fetch_index(tid);
+        fetch_point();
         for (int r0 = 0; r0 < total; r0 += ST_ROWS) {
             // ---- build: this thread's row (fetched during the previous tile)
             const int ci = nci;
@@ -231,10 +239,11 @@ sa_tc_kernel(const SaTcParams a) {
             const int ci_up = __shfl_up_sync(0xffffffffu, ci, 1);
             const unsigned starts = __ballot_sync(0xffffffffu, lane == 0 || ci != ci_up);
             s_ci[tid] = (uint8_t)ci;
-            fetch_row(r0 + ST_ROWS + tid);
+            fetch_index(r0 + ST_ROWS + tid);
             // ---- layer 1: D[rows, 16] at TMEM columns 0..15
             run_mma([&] { ptx::mma_f16_ss_warp(tmem_base, st_sdesc(act_a, ST_LBO), st_sdesc(w1_a, 16 * 16), ID16, 0u); });
             hidden_epilogue(tlane);
+            fetch_point();                       // the index fetched after the build has arrived by now
             // ---- layer 2: columns 16..31
             run_mma([&] {
 #pragma unroll
