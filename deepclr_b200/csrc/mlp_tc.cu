@@ -649,12 +649,13 @@ constexpr int HEAD_LAYERS = 5;
 // 64 x 5 stages 0.184 ms | 80 x 4 0.174 | 96 x 3 0.168 | 96 x 2 0.192 | 128 x 2 0.177 | 112 x 3 0.163 (ONE issuing warp).
 // With two issuing warps (below) stage s belongs to warp s % 2 (tile `it` of the stream sits in stage it % STAGES and
 // belongs to warp it % 2, so STAGES must be even): a consumer then never waits on a stage whose previous occupant was
-// another warp's, and the 1-bit phase parity of its mbarrier cannot alias.  4 x 20 KB.
+// another warp's, and the 1-bit phase parity of its mbarrier cannot alias.  6 x 12 KB.
+// Measured with two issuing warps: 80 x 4 0.1427 ms | 64 x 4 0.151 | **48 x 6 0.140** | 32 x 10 0.160 | 112 x 2 0.185.
 #ifndef DCLR_HEAD_KT
-#define DCLR_HEAD_KT 80
-#define DCLR_HEAD_STAGES 4
+#define DCLR_HEAD_KT 48
+#define DCLR_HEAD_STAGES 6
 #endif
-constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 80 = 20 KB)
+constexpr int HEAD_KT = DCLR_HEAD_KT;            // K elements per streamed weight tile (128 rows x 48 = 12 KB)
 constexpr int HEAD_STAGES = DCLR_HEAD_STAGES;
 constexpr int HEAD_TILE_BYTES = 128 * HEAD_KT * 2;
 constexpr int HEAD_EPI_WARPS = 8;                // 4 TMEM lane quarters x 2 column halves
