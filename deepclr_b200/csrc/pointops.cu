@@ -434,6 +434,10 @@ knn_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx, int
 constexpr int KNNF_WARPS = 8;
 constexpr int KNNF_QPW = 4;                 // queries per warp (share the staged candidates)
 constexpr int KNNF_CAP = 128;               // compacted candidates per query
+#ifndef DCLR_KNN_TWOMIN_K
+#define DCLR_KNN_TWOMIN_K 24
+#endif
+constexpr int KNNF_TWOMIN_K = DCLR_KNN_TWOMIN_K;   // above this k the threshold uses two minima per lane
 
 template <int KPL>
 __global__ void __launch_bounds__(KNNF_WARPS * 32)
@@ -490,7 +494,7 @@ knn_fast_kernel(const float *__restrict__ x, const float *__restrict__ y, int Nx
         // survivors, the slow selection below); there every lane offers its TWO smallest distances instead, and the
         // k-th smallest of those 64 real candidates is close to the true k-th distance (~35 survivors).
         uint32_t v = __float_as_uint(lmin), v2 = 0xffffffffu, T = 0;
-        if (k > 24) {                                           // warp-uniform
+        if (k > KNNF_TWOMIN_K) {                                // warp-uniform
             float m1 = INFINITY, m2 = INFINITY;
 #pragma unroll
             for (int i = 0; i < KPL; ++i) {
