@@ -153,7 +153,7 @@ class ClockSampler(threading.Thread):
     def _run_nvml(self):
         while not self._halt.is_set():
             self._sample_nvml()
-            self._halt.wait(0.001)
+            self._halt.wait(0.002)
 
     def run(self):
         try:
@@ -369,6 +369,15 @@ def run_native(args, rank, world, local_rank):
                     forward(i)
             torch.cuda.synchronize(dev)
         run_resident(warmup)
+        # short steps (a few pairs per GPU): W steps are ~1 ms of GPU work, not enough to reach steady clocks and a warm
+        # allocator on every rank -- keep going, untimed, until 40 ms have passed (the timed K steps are unchanged)
+        t_warm = time.perf_counter()
+        while time.perf_counter() - t_warm < 0.04:
+            run_resident(max(warmup, lanes))
+            torch.cuda.synchronize(dev)
+        import gc
+        gc.collect()
+        gc.disable()                    # no collector pause inside a timed region of a few milliseconds
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         sampler = ClockSampler(local_rank) if rank == 0 else None
         barrier()
@@ -386,6 +395,9 @@ def run_native(args, rank, world, local_rank):
         # inside the timed region (deepclr_b200.models.HostPipeline, forward replayed from CUDA graphs)
         pipe = HostPipeline(model, depth=2 * lanes, use_cuda_graph=use_graph, replicas=lanes)
         pipe.run_all(host[i % ROTATE] for i in range(max(2 * lanes + 1, warmup // 2)))
+        t_warm = time.perf_counter()
+        while time.perf_counter() - t_warm < 0.04:                       # as above: untimed, until 40 ms have passed
+            pipe.run_all(host[i % ROTATE] for i in range(2 * lanes + 1))
         pipe.h2d_bytes = pipe.d2h_bytes = 0
         barrier()
         e0.record()
@@ -393,6 +405,7 @@ def run_native(args, rank, world, local_rank):
         e1.record()
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+        gc.enable()
         assert len(outs) == steps and all(torch.isfinite(o).all() for o in outs)
         e2e = {'ms_per_step': ms_e2e / steps, 'h2d_bytes_per_step': pipe.h2d_bytes // steps,
                'd2h_bytes_per_step': pipe.d2h_bytes // steps,
